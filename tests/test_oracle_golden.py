@@ -1,0 +1,122 @@
+"""Pin the numpy oracle (oracle/corr_oracle.py) and the torch-op port
+(oracle/torch_port.py) against tensors frozen from the reference's own
+CorrBlock (tests/golden/, made by oracle/make_golden.py)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import corr_oracle as O
+from oracle import torch_port as P
+
+KINDS = ["rand", "int", "far", "edge"]
+
+
+def test_pyramid_matches_reference(golden):
+    pyr = O.corr_pyramid(golden["fmap1"], golden["fmap2"], 4)
+    for l, p in enumerate(pyr):
+        ref = golden[f"pyr{l}"]
+        assert p.shape == ref.shape
+        np.testing.assert_allclose(p, ref, rtol=1e-5, atol=2e-5)
+
+
+def test_pyramid_dims_floor(golden):
+    H, W = golden["fmap1"].shape[-2:]
+    dims = O.pyramid_dims(H, W, 4)
+    for l, (h, w) in enumerate(dims):
+        assert golden[f"pyr{l}"].shape[1:] == (h, w)
+
+
+@pytest.mark.parametrize("kind", KINDS)
+def test_lookup_matches_reference(golden, kind):
+    # use the reference's own pyramid so this isolates the lookup
+    pyr = [golden[f"pyr{l}"] for l in range(4)]
+    out = O.window_lookup(pyr, golden[f"coords_{kind}"], int(golden["radius"]))
+    ref = golden[f"out_{kind}"]
+    assert out.shape == ref.shape and out.dtype == np.float32
+    # the reference's normalise/denormalise round trip moves coordinates by ~1 ulp
+    np.testing.assert_allclose(out, ref, rtol=1e-4, atol=2e-5)
+    if kind == "far":
+        assert not out.any()
+
+
+def test_lookup_channel_order(golden):
+    """channel l*n*n + i*n + j samples (x/2^l + i - r, y/2^l + j - r)."""
+    r = int(golden["radius"])
+    n = 2 * r + 1
+    pyr = [golden[f"pyr{l}"] for l in range(4)]
+    coords = golden["coords_int"]
+    B, _, H, W = coords.shape
+    out = golden["out_int"]
+    rng = np.random.default_rng(0)
+    for _ in range(200):
+        b, y, x = rng.integers(B), rng.integers(H), rng.integers(W)
+        i, j = rng.integers(n), rng.integers(n)
+        X = int(coords[b, 0, y, x]) + i - r
+        Y = int(coords[b, 1, y, x]) + j - r
+        q = (b * H + y) * W + x
+        want = pyr[0][q, Y, X] if (0 <= X < W and 0 <= Y < H) else 0.0
+        assert abs(out[b, i * n + j, y, x] - want) < 1e-5
+
+
+def test_lookup_backward_matches_autograd(golden):
+    r = int(golden["radius"])
+    pyr = O.corr_pyramid(golden["fmap1"].astype(np.float64), golden["fmap2"].astype(np.float64), 4)
+    dpyr, dcoords = O.window_lookup_backward(pyr, golden["coords_rand"], r, golden["grad_out"])
+    for l in range(1, 4):
+        np.testing.assert_allclose(dpyr[l], golden[f"dpyr{l}"], rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(dpyr[0].sum(axis=2), golden["dpyr0_rowsum"], rtol=1e-4, atol=1e-4)
+    np.testing.assert_allclose(dcoords, golden["dcoords"], rtol=2e-3, atol=2e-3)
+    d1, d2 = O.pyramid_backward(dpyr, golden["fmap1"], golden["fmap2"])
+    np.testing.assert_allclose(d1, golden["dfmap1"], rtol=1e-3, atol=1e-4)
+    np.testing.assert_allclose(d2, golden["dfmap2"], rtol=1e-3, atol=1e-4)
+
+
+def test_alt_path_equals_default_path(golden):
+    """AlternateCorrBlock is mathematically the default path;
+    the reference extension is CUDA-only, so it is anchored on CorrBlock."""
+    r = int(golden["radius"])
+    f1, f2 = golden["fmap1"][:1], golden["fmap2"][:1]
+    for kind in ("rand", "edge"):
+        c = golden[f"coords_{kind}"][:1]
+        out = O.alt_block_lookup(f1, f2, c, 4, r)
+        np.testing.assert_allclose(out, golden[f"out_{kind}"][:1], rtol=1e-4, atol=3e-5)
+
+
+def test_alt_backward_is_transpose_of_forward():
+    """<alt_forward(f1,f2), g> differentiated numerically matches alt_backward;
+    coords_grad is identically zero as in the reference kernel."""
+    rng = np.random.default_rng(3)
+    B, H, W, C, r = 1, 5, 6, 4, 2
+    f1 = rng.standard_normal((B, H, W, C)).astype(np.float32)
+    f2 = rng.standard_normal((B, 4, 5, C)).astype(np.float32)
+    coords = (rng.uniform(-1, 5, (B, 1, H, W, 2))).astype(np.float32)
+    g = rng.standard_normal((B, 1, (2 * r + 1) ** 2, H, W)).astype(np.float32)
+    g1, g2, gc = O.alt_backward(f1, f2, coords, g, r)
+    assert not gc.any()
+    eps = 1e-2
+    for arr, grad, which in ((f1, g1, 0), (f2, g2, 1)):
+        for _ in range(5):
+            idx = tuple(rng.integers(s) for s in arr.shape)
+            a = arr.copy(); a[idx] += eps
+            b = arr.copy(); b[idx] -= eps
+            fa = O.alt_forward(a if which == 0 else f1, a if which == 1 else f2, coords, r)
+            fb = O.alt_forward(b if which == 0 else f1, b if which == 1 else f2, coords, r)
+            num = ((fa.astype(np.float64) - fb) * g).sum() / (2 * eps)
+            assert abs(num - grad[idx]) < 2e-2 * max(1.0, abs(num))
+
+
+@pytest.mark.parametrize("kind", KINDS)
+def test_torch_port_matches_reference(golden, kind):
+    f1 = torch.from_numpy(golden["fmap1"])
+    f2 = torch.from_numpy(golden["fmap2"])
+    pyr = P.build_pyramid(f1, f2, 4)
+    for l, p in enumerate(pyr):
+        np.testing.assert_allclose(p[:, 0].numpy(), golden[f"pyr{l}"], rtol=1e-5, atol=2e-5)
+    out = P.lookup(pyr, torch.from_numpy(golden[f"coords_{kind}"]), int(golden["radius"]))
+    np.testing.assert_allclose(out.numpy(), golden[f"out_{kind}"], rtol=1e-5, atol=1e-5)
+
+
+def test_coords_grid_convention():
+    g = O.coords_grid(2, 3, 5)
+    assert g.shape == (2, 2, 3, 5)
+    assert g[0, 0, 1, 4] == 4 and g[0, 1, 1, 4] == 1
