@@ -1,0 +1,377 @@
+#!/usr/bin/env python
+"""Benchmark of RAFT's correlation hot path on B200 (contract: see DESIGN.md "Measurement").
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+One STEP = one pass of the hot path over one batch of synthetic frame pairs at
+the Sintel shape (1/8-resolution features 55 x 128 x 256, BASELINE.json
+configs[1]): volume build + 4-level pyramid, then 12 windowed lookups (r = 4)
+at 12 different coordinate fields.  `value` = frame pairs per second over all
+ranks with inputs resident in HBM; `e2e` = the same work through the public
+CorrBlock API from pinned HOST buffers (features and coordinates copied in,
+all 12 lookup outputs copied out) inside the timed region.
+
+For N > 1 launch with torch.distributed.run; ranks shard the frame pairs
+(weak scaling, no collective on the data path).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+H, W, D, LEVELS, RADIUS, ITERS = 55, 128, 256, 4, 4, 12
+N = H * W
+PYR_ELEMS = sum(N * (H >> l) * (W >> l) for l in range(LEVELS))          # 65 331 200
+BUILD_FLOPS = 2.0 * N * N * D                                           # 25.376 GFLOP / pair
+WORKLOAD = "corrblock_microbench_55x128x256_L4_r4_build+12lookups"
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {"hbm_gbs": d["hbm_gbs"], "bf16_tflops": d["bf16_tflops"],
+                "bf16_tflops_sustained": d.get("bf16_tflops_sustained", d["bf16_tflops"]), "source": "measured"}
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
+
+
+def make_inputs(batch, device, seed):
+    """Seeded synthetic features and 12 coordinate fields (grid + N(0, 5^2) flow)."""
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    f1 = torch.randn(batch, D, H, W, generator=g)
+    f2 = torch.randn(batch, D, H, W, generator=g)
+    ys, xs = torch.meshgrid(torch.arange(H), torch.arange(W), indexing="ij")
+    grid = torch.stack([xs, ys], 0).float()[None]
+    coords = [grid + 5.0 * torch.randn(batch, 2, H, W, generator=g) for _ in range(ITERS)]
+    if device is not None:
+        f1, f2 = f1.to(device), f2.to(device)
+        coords = [c.to(device) for c in coords]
+    return f1, f2, coords
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(self.index)],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            parts = [p.strip() for p in ln.split(",")]
+            if len(parts) < 6:
+                continue
+            try:
+                sm.append(float(parts[0])); mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, parts[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def cpu_reference_pairs_per_s(budget_s, max_pairs):
+    """The reference's CPU path (same torch library calls, oracle/torch_port.py)
+    timed on the host cores over a bounded sample of the workload."""
+    from oracle import torch_port as P
+    torch.set_num_threads(os.cpu_count() or 1)
+    f1, f2, coords = make_inputs(1, None, seed=0)
+    with torch.no_grad():
+        P.hot_path(f1, f2, coords[:1], RADIUS, LEVELS)            # warm-up (thread pools, allocator)
+        times = []
+        t_start = time.perf_counter()
+        while len(times) < max_pairs and (len(times) < 2 or time.perf_counter() - t_start < budget_s):
+            t0 = time.perf_counter()
+            P.hot_path(f1, f2, coords, RADIUS, LEVELS)
+            times.append(time.perf_counter() - t0)
+    return len(times) / sum(times), len(times), torch.get_num_threads()
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    per_step = 1
+    _ = per_step
+    from oracle import torch_port as P
+    torch.set_num_threads(os.cpu_count() or 1)
+    f1, f2, coords = make_inputs(1, None, seed=0)
+    with torch.no_grad():
+        for _ in range(max(args.warmup, 1)):
+            P.hot_path(f1, f2, coords, RADIUS, LEVELS)
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            P.hot_path(f1, f2, coords, RADIUS, LEVELS)
+        dt = time.perf_counter() - t0
+    v = args.steps / dt
+    cores = torch.get_num_threads()
+    line = {
+        "impl": "reference", "metric": "frame_pairs_per_s_corr_hot_path_55x128x256_12iters", "value": v,
+        "unit": "pairs/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": max(args.warmup, 1),
+        "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "pairs_per_step": 1, "device": "host CPU"},
+        "cpu_baseline": {"value": v, "unit": "pairs/s", "cores": cores, "kind": "port",
+                         "sample": "1 pair per step (build + 12 lookups), reference's torch CPU calls via oracle/torch_port.py"},
+        "e2e": {"value": v, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=16, help="frame pairs per GPU per step")
+    ap.add_argument("--storage", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU baseline work")
+    ap.add_argument("--no-extras", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the correlation path has no CPU fallback")
+    import raft_stir_b200 as R
+    from raft_stir_b200 import _lib
+    _lib.lib()
+
+    device = torch.device("cuda", local_rank)
+    torch.cuda.set_device(device)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=device)
+
+    B = args.batch
+    f1, f2, coords = make_inputs(B, device, seed=1000 + rank)
+    stream = torch.cuda.current_stream()
+    es = 2 if args.storage == "bf16" else 4
+
+    def step(rec=None):
+        if rec is not None:
+            rec.append(torch.cuda.Event(enable_timing=True)); rec[-1].record(stream)
+        blk = R.CorrBlock(f1, f2, LEVELS, RADIUS, storage=args.storage)
+        if rec is not None:
+            rec.append(torch.cuda.Event(enable_timing=True)); rec[-1].record(stream)
+        out = None
+        for c in coords:
+            out = blk(c)
+            if rec is not None:
+                rec.append(torch.cuda.Event(enable_timing=True)); rec[-1].record(stream)
+        return out
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    with torch.no_grad():
+        for _ in range(args.warmup):
+            step()
+        barrier()
+        sampler = ClockSampler(local_rank)
+        sampler.start()
+        recs = []
+        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record(stream)
+        for _ in range(args.steps):
+            r = []
+            step(r)
+            recs.append(r)
+        e1.record(stream)
+        barrier()
+        clocks = sampler.stop()
+    ms = e0.elapsed_time(e1)
+    if dist is not None:
+        tms = torch.tensor([ms], device=device)
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+        ms = float(tms.item())
+
+    # per-kernel durations from the events recorded inside the timed region
+    build_ms = [r[0].elapsed_time(r[1]) for r in recs]
+    look_ms = [r[i].elapsed_time(r[i + 1]) for r in recs for i in range(1, 1 + ITERS)]
+    build_avg, look_avg = statistics.mean(build_ms), statistics.mean(look_ms)
+
+    pk = peaks()
+    look_bytes = B * N * (LEVELS * (2 * RADIUS + 2) ** 2 * es + 8 + LEVELS * (2 * RADIUS + 1) ** 2 * 4)
+    build_bytes = B * (2 * N * D * 4 + PYR_ELEMS * es)       # fp32 features in, pyramid out (repack traffic not counted)
+    look_gbs = look_bytes / (look_avg * 1e-3) / 1e9
+    build_gbs = build_bytes / (build_avg * 1e-3) / 1e9
+    build_tf = B * BUILD_FLOPS / (build_avg * 1e-3) / 1e12
+    lookups_dominate = ITERS * look_avg >= build_avg
+    if lookups_dominate:
+        roof = {"kernel": "lookup_fwd_kernel", "bound": "hbm", "achieved": look_gbs, "peak": pk["hbm_gbs"], "unit": "GB/s",
+                "frac": look_gbs / pk["hbm_gbs"], "traffic": None, "peak_source": pk["source"],
+                "algorithmic_bytes_per_launch": look_bytes, "avg_launch_ms": look_avg}
+    else:
+        roof = {"kernel": "build_pyramid_tc_kernel(+pack)", "bound": "hbm", "achieved": build_gbs, "peak": pk["hbm_gbs"],
+                "unit": "GB/s", "frac": build_gbs / pk["hbm_gbs"], "traffic": None, "peak_source": pk["source"],
+                "algorithmic_bytes_per_launch": build_bytes, "avg_launch_ms": build_avg}
+    kernels = {
+        "lookup_fwd": {"avg_ms": look_avg, "GB/s": look_gbs, "frac_hbm": look_gbs / pk["hbm_gbs"], "share_of_step": ITERS * look_avg / (ITERS * look_avg + build_avg)},
+        "build(pack+tcgen05)": {"avg_ms": build_avg, "GB/s": build_gbs, "frac_hbm": build_gbs / pk["hbm_gbs"], "TFLOP/s": build_tf,
+                                "frac_tensor": build_tf / pk["bf16_tflops_sustained"], "share_of_step": build_avg / (ITERS * look_avg + build_avg)},
+    }
+
+    # ---- end to end through the public API from pinned host buffers
+    e2e = None
+    with torch.no_grad():
+        hf1, hf2 = f1.cpu().pin_memory(), f2.cpu().pin_memory()
+        hcoords = [c.cpu().pin_memory() for c in coords]
+        nch = LEVELS * (2 * RADIUS + 1) ** 2
+        houts = [torch.empty(B, nch, H, W, dtype=torch.float32).pin_memory() for _ in range(ITERS)]
+        copy_stream = torch.cuda.Stream(device)
+
+        def e2e_step():
+            d1 = hf1.to(device, non_blocking=True)
+            d2 = hf2.to(device, non_blocking=True)
+            blk = R.CorrBlock(d1, d2, LEVELS, RADIUS, storage=args.storage)
+            for i in range(ITERS):
+                c = hcoords[i].to(device, non_blocking=True)
+                o = blk(c)
+                ev = torch.cuda.Event(); ev.record(stream)
+                copy_stream.wait_event(ev)
+                with torch.cuda.stream(copy_stream):
+                    houts[i].copy_(o, non_blocking=True)
+                o.record_stream(copy_stream)
+            stream.wait_stream(copy_stream)
+
+        e2e_step()
+        barrier()
+        t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
+        t0.record(stream)
+        for _ in range(args.e2e_steps):
+            e2e_step()
+        t1.record(stream)
+        barrier()
+        e2e_ms = t0.elapsed_time(t1)
+        if dist is not None:
+            tms = torch.tensor([e2e_ms], device=device)
+            dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+            e2e_ms = float(tms.item())
+        e2e = {"value": world * B * args.e2e_steps / (e2e_ms * 1e-3), "unit": "pairs/s",
+               "h2d_bytes_per_step": int(2 * B * D * N * 4 + ITERS * B * 2 * N * 4),
+               "d2h_bytes_per_step": int(ITERS * B * nch * N * 4), "steps": args.e2e_steps,
+               "api": "raft_stir_b200.CorrBlock(fmap1, fmap2)(coords) x12, pinned host in / pinned host out"}
+
+    # ---- CPU baseline (rank 0, N = 1 only) and extras
+    cpu = None
+    extras = {}
+    if rank == 0 and world == 1:
+        v, npairs, cores = cpu_reference_pairs_per_s(args.cpu_budget, max_pairs=40)
+        cpu = {"value": v, "unit": "pairs/s", "cores": cores, "kind": "port",
+               "sample": f"{npairs} pairs of {WORKLOAD} via oracle/torch_port.py (the reference's torch CPU calls)"}
+        if not args.no_extras:
+            extras = run_extras(R, device, args, pk)
+
+    if rank == 0:
+        line = {
+            "metric": "frame_pairs_per_s_corr_hot_path_55x128x256_12iters",
+            "value": world * B * args.steps / (ms * 1e-3), "unit": "pairs/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "bf16" if args.storage == "bf16" else "f32",
+            "data": "synthetic",
+            "config": {"workload": WORKLOAD, "pairs_per_gpu_per_step": B, "volume_storage": args.storage,
+                       "build_math": "bf16 tcgen05, fp32 accumulate", "l2": "working set per step (pyramid %.0f MB) exceeds the 126 MB L2" % (B * PYR_ELEMS * es / 1e6),
+                       "parallelism": f"pairs sharded over {world} rank(s), no collective"},
+            "roofline": roof, "kernels": kernels, "cpu_baseline": cpu, "e2e": e2e,
+            "gpu_launches": world * args.steps * (2 + ITERS), "clocks": clocks, "extras": extras,
+        }
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def run_extras(R, device, args, pk):
+    """Secondary measurements (not the headline): single-pair latency, training
+    direction, on-the-fly path.  CUDA events, warm, reported as-is."""
+    out = {}
+    stream = torch.cuda.current_stream()
+
+    def timeit(fn, reps):
+        fn(); torch.cuda.synchronize()
+        a = torch.cuda.Event(enable_timing=True); b = torch.cuda.Event(enable_timing=True)
+        a.record(stream)
+        for _ in range(reps):
+            fn()
+        b.record(stream); torch.cuda.synchronize()
+        return a.elapsed_time(b) / reps
+
+    try:
+        with torch.no_grad():
+            f1, f2, coords = make_inputs(1, device, seed=7)
+            out["b1_build_ms"] = timeit(lambda: R.CorrBlock(f1, f2, LEVELS, RADIUS, storage=args.storage), 20)
+            blk = R.CorrBlock(f1, f2, LEVELS, RADIUS, storage=args.storage)
+            out["b1_lookup_ms"] = timeit(lambda: blk(coords[0]), 50)
+            out["b1_build_fp32_simt_ms"] = timeit(lambda: R.CorrBlock(f1, f2, LEVELS, RADIUS, storage="fp32", math="fp32"), 3)
+            alt = R.AlternateCorrBlock(f1, f2, LEVELS, RADIUS)
+            out["b1_alt_lookup_ms"] = timeit(lambda: alt(coords[0]), 10)
+        # training direction at the FlyingChairs shape (config 5): 46x62, batch 10
+        g = torch.Generator(device="cpu").manual_seed(3)
+        Bc, Hc, Wc = 10, 46, 62
+        a1 = torch.randn(Bc, D, Hc, Wc, generator=g).to(device).requires_grad_(True)
+        a2 = torch.randn(Bc, D, Hc, Wc, generator=g).to(device).requires_grad_(True)
+        cc = [R.coords_grid(Bc, Hc, Wc, device) + 3 * torch.randn(Bc, 2, Hc, Wc, device=device) for _ in range(ITERS)]
+
+        def train_step():
+            a1.grad = None; a2.grad = None
+            blk = R.CorrBlock(a1, a2, LEVELS, RADIUS, storage=args.storage)
+            loss = sum(blk(c).sum() for c in cc)
+            loss.backward()
+        out["chairs_b10_fwd_bwd_ms"] = timeit(train_step, 5)
+    except Exception as e:  # extras must never sink the headline
+        out["error"] = f"{type(e).__name__}: {e}"
+    return out
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,173 @@
+/*
+ * raft_corr.h -- C ABI of libraftcorr: RAFT's correlation hot path on B200 (sm_100a).
+ *
+ * Drop-in boundary for athaddius/RAFT_STIR (paths below are relative to that
+ * repository).  Plain pointers and sizes only; every pointer is a DEVICE
+ * pointer on the current CUDA device unless said otherwise.  The library
+ * allocates nothing in these calls: outputs and workspaces are the caller's.
+ * All launches are asynchronous on `stream`.
+ *
+ * Return value: 0 on success, a negative RC_E* code on failure;
+ * rc_last_error() then returns a thread-local message.  No exceptions cross
+ * this boundary.  There is no CPU path: without a CUDA device every compute
+ * entry point fails with RC_ECUDA.
+ */
+#ifndef RAFT_CORR_H_
+#define RAFT_CORR_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define RC_API __attribute__((visibility("default")))
+#else
+#define RC_API
+#endif
+
+#define RC_ABI_VERSION 1
+#define RC_MAX_LEVELS 6
+
+/* error codes */
+#define RC_OK 0
+#define RC_EINVAL (-1)   /* bad argument (null pointer, size, dtype, radius ...) */
+#define RC_ECUDA (-2)    /* a CUDA runtime / driver call failed */
+#define RC_ESIZE (-3)    /* workspace or static scratch too small for the request */
+
+/* storage type of the correlation volume / pyramid */
+#define RC_VOL_F32 0
+#define RC_VOL_BF16 1
+
+/* arithmetic used to form the feature dot products of the volume build */
+#define RC_MATH_F32 0    /* CUDA-core fp32 FMA: what the reference's SGEMM does */
+#define RC_MATH_BF16 1   /* tcgen05 kind::f16, bf16 operands, fp32 accumulate in TMEM */
+#define RC_MATH_TF32 2   /* tcgen05 kind::tf32, fp32 operands read as tf32 */
+
+typedef struct CUstream_st *rc_stream_t;   /* == cudaStream_t */
+
+/*
+ * Memory layout of the pooled correlation pyramid (all levels in ONE buffer).
+ * Level l holds, for every query (b, q), a slab of H[l] rows with a padded
+ * row pitch:  element (b, q, y, x) of level l lives at
+ *     offset[l] + ((size_t)b * N + q) * slab[l] + y * pitch[l] + x.
+ * H[l] = H >> l and W[l] = W >> l, which is what three floor-truncating
+ * avg_pool2d(2, 2) calls give (core/corr.py:24-27).  Units are elements.
+ */
+typedef struct rc_layout {
+  int32_t num_levels;
+  int32_t B, N;                    /* N = H * W queries per pair */
+  int32_t H[RC_MAX_LEVELS];
+  int32_t W[RC_MAX_LEVELS];
+  int32_t pitch[RC_MAX_LEVELS];
+  int64_t slab[RC_MAX_LEVELS];
+  int64_t offset[RC_MAX_LEVELS];
+  int64_t total_elems;             /* size of the whole buffer, elements */
+  int32_t elem_bytes;              /* 4 (RC_VOL_F32) or 2 (RC_VOL_BF16) */
+} rc_layout;
+
+RC_API int rc_abi_version(void);
+RC_API const char *rc_last_error(void);
+
+/* Fills *out for a pyramid of `num_levels` levels over B pairs of H x W
+ * feature maps.  Host-only arithmetic; needs no GPU. */
+RC_API int rc_pyramid_layout(int B, int H, int W, int num_levels, int vol_dtype, rc_layout *out);
+
+/* Bytes of scratch rc_build_pyramid needs for its repacked feature maps
+ * (0 for RC_MATH_F32).  Host-only arithmetic. */
+RC_API int64_t rc_build_workspace_bytes(int B, int D, int H, int W, int math);
+
+/*
+ * Volume build + pooled pyramid.  Replaces CorrBlock.corr (core/corr.py:52-60:
+ * matmul, then a separate / sqrt(D) pass) and the three avg_pool2d calls of
+ * CorrBlock.__init__ (core/corr.py:21-27).
+ *   fmap1, fmap2 : fp32 [B, D, H, W] contiguous (NCHW, as RAFT.forward passes
+ *                  them, core/raft.py:102-107)
+ *   pyramid      : out, rc_layout of (B, H, W, num_levels, vol_dtype)
+ *   workspace    : >= rc_build_workspace_bytes(...) bytes, 256-byte aligned
+ */
+RC_API int rc_build_pyramid(const float *fmap1, const float *fmap2, int B, int D, int H, int W,
+                     int num_levels, int vol_dtype, int math, void *pyramid,
+                     void *workspace, size_t workspace_bytes, rc_stream_t stream);
+
+/*
+ * Windowed bilinear lookup over all levels in one launch.  Replaces
+ * CorrBlock.__call__ (core/corr.py:29-50) together with bilinear_sampler /
+ * F.grid_sample(align_corners=True, zeros padding) (core/utils/utils.py:57-65).
+ *   coords : fp32 [B, 2, H, W], channel 0 = x, 1 = y (core/utils/utils.py:74-77)
+ *   out    : fp32 [B, num_levels*(2r+1)^2, H, W]; channel l*(2r+1)^2 + i*(2r+1) + j
+ *            samples level l at (x/2^l + i - r, y/2^l + j - r)
+ *   radius : 1..4
+ */
+RC_API int rc_lookup_fwd(const void *pyramid, int vol_dtype, const float *coords, int B, int H, int W,
+                  int num_levels, int radius, float *out, rc_stream_t stream);
+
+/*
+ * Backward of rc_lookup_fwd: what autograd of F.grid_sample yields at
+ * core/utils/utils.py:65 for every level, in one launch.
+ *   grad_out     : fp32 [B, num_levels*(2r+1)^2, H, W]
+ *   grad_pyramid : fp32 pyramid, rc_layout(..., RC_VOL_F32); ACCUMULATED into (+=),
+ *                  so the 12 GRU iterations can share one buffer; may be NULL
+ *   grad_coords  : fp32 [B, 2, H, W], overwritten; may be NULL
+ */
+RC_API int rc_lookup_bwd(const void *pyramid, int vol_dtype, const float *coords, const float *grad_out,
+                  int B, int H, int W, int num_levels, int radius, float *grad_pyramid,
+                  float *grad_coords, rc_stream_t stream);
+
+/* Bytes of scratch rc_build_bwd needs. Host-only arithmetic. */
+RC_API int64_t rc_build_bwd_workspace_bytes(int B, int D, int H, int W, int num_levels);
+
+/*
+ * Backward of rc_build_pyramid: transposes of the three avg_pool2d calls and of
+ * the matmul of core/corr.py:58-60 (what autograd runs for train.py:175).
+ *   grad_pyramid   : fp32 pyramid (RC_VOL_F32 layout), read only
+ *   dfmap1, dfmap2 : fp32 [B, D, H, W], overwritten
+ */
+RC_API int rc_build_bwd(const float *grad_pyramid, const float *fmap1, const float *fmap2, int B, int D,
+                 int H, int W, int num_levels, float *dfmap1, float *dfmap2, void *workspace,
+                 size_t workspace_bytes, rc_stream_t stream);
+
+/*
+ * On-the-fly correlation, one level: same contract as alt_cuda_corr.forward
+ * (alt_cuda_corr/correlation.cpp:23-33 -> correlation_kernel.cu:260-286,
+ * kernel :18-119).  Never materialises the volume.
+ *   fmap1  : fp32 [B, H1, W1, C]      fmap2 : fp32 [B, H2, W2, C]
+ *   coords : fp32 [B, Nc, H1, W1, 2]  (x, y) in fmap2 pixels
+ *   corr   : out fp32 [B, Nc, (2r+1)^2, H1, W1], overwritten (the reference
+ *            zero-fills then accumulates, :273); NOT scaled by 1/sqrt(C)
+ */
+RC_API int rc_alt_fwd(const float *fmap1, const float *fmap2, const float *coords, int B, int H1, int W1,
+               int H2, int W2, int C, int Nc, int radius, float *corr, rc_stream_t stream);
+
+/*
+ * Same contract as alt_cuda_corr.backward (correlation.cpp:36-48 ->
+ * correlation_kernel.cu:288-324, kernel :122-256).
+ *   fmap1_grad [B,H1,W1,C], fmap2_grad [B,H2,W2,C], coords_grad [B,Nc,H1,W1,2]:
+ *   all overwritten; coords_grad is zero-filled, as in the reference, whose
+ *   kernel never writes it (:307).
+ */
+RC_API int rc_alt_bwd(const float *fmap1, const float *fmap2, const float *coords, const float *corr_grad,
+               int B, int H1, int W1, int H2, int W2, int C, int Nc, int radius, float *fmap1_grad,
+               float *fmap2_grad, float *coords_grad, rc_stream_t stream);
+
+/*
+ * AlternateCorrBlock.__call__ in one launch (core/corr.py:74-91): all levels,
+ * NCHW features read in place, 1/sqrt(D) applied.
+ *   fmap1      : fp32 [B, D, H, W]
+ *   fmap2_pyr  : fp32, level l is [B, H>>l, W>>l, D] (NHWC) at element offset
+ *                f2_offset[l]; produce it with rc_alt_pool_features
+ *   coords     : fp32 [B, 2, H, W];  out: fp32 [B, num_levels*(2r+1)^2, H, W]
+ */
+RC_API int64_t rc_alt_feature_pyramid_elems(int B, int D, int H, int W, int num_levels, int64_t *f2_offset);
+RC_API int rc_alt_pool_features(const float *fmap1, const float *fmap2, int B, int D, int H, int W,
+                         int num_levels, float *fmap1_nhwc, float *fmap2_pyr, rc_stream_t stream);
+RC_API int rc_alt_lookup_fwd(const float *fmap1_nhwc, const float *fmap2_pyr, const float *coords, int B,
+                      int D, int H, int W, int num_levels, int radius, float *out,
+                      rc_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RAFT_CORR_H_ */

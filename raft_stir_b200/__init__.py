@@ -1,0 +1,12 @@
+"""raft_stir_b200 -- RAFT's correlation hot path on B200 (sm_100a).
+
+Drop-in replacements for the reference's `CorrBlock` / `AlternateCorrBlock`
+(core/corr.py) and its optional `alt_cuda_corr` extension, backed by
+hand-written CUDA kernels behind the C ABI declared in include/raft_corr.h.
+There is no CPU path: constructing a block without the compiled library or
+without a CUDA tensor raises.
+"""
+from .corr import AlternateCorrBlock, CorrBlock, coords_grid, install_into  # noqa: F401
+from . import alt_cuda_corr  # noqa: F401
+
+__all__ = ["CorrBlock", "AlternateCorrBlock", "alt_cuda_corr", "coords_grid", "install_into"]

@@ -1,0 +1,269 @@
+"""Drop-in `CorrBlock` / `AlternateCorrBlock` (reference: core/corr.py).
+
+Same constructor `(fmap1, fmap2, num_levels=4, radius=4)`, same call
+`corr_fn(coords) -> [B, num_levels*(2r+1)^2, H, W] fp32`, same attributes
+(`num_levels`, `radius`, `corr_pyramid` / `pyramid`), so `RAFT.forward`
+(core/raft.py:104-107, :124) runs unchanged once the two names are swapped:
+
+    import raft, raft_stir_b200
+    raft_stir_b200.install_into(raft)
+
+Everything numeric happens in libraftcorr.so through the C ABI
+(include/raft_corr.h); torch is used for device memory, the current stream and
+autograd bookkeeping only.  CPU tensors are rejected: there is no fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import List, Optional
+
+import torch
+
+from . import _lib
+from ._lib import RaftCorrError, check
+
+_STORAGE = {"bf16": _lib.RC_VOL_BF16, "fp32": _lib.RC_VOL_F32}
+_MATH = {"bf16": _lib.RC_MATH_BF16, "fp32": _lib.RC_MATH_F32}
+_TORCH_DT = {_lib.RC_VOL_BF16: torch.bfloat16, _lib.RC_VOL_F32: torch.float32}
+
+
+def _stream(t: torch.Tensor) -> int:
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+def _require_cuda_f32(t: torch.Tensor, name: str) -> torch.Tensor:
+    if not isinstance(t, torch.Tensor):
+        raise RaftCorrError(f"{name} must be a torch.Tensor")
+    if not t.is_cuda:
+        raise RaftCorrError(f"{name} must be a CUDA tensor (libraftcorr has no CPU path)")
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t.contiguous()
+
+
+def coords_grid(batch: int, ht: int, wd: int, device) -> torch.Tensor:
+    """[B,2,H,W], channel 0 = x, channel 1 = y (core/utils/utils.py:74-77)."""
+    ys, xs = torch.meshgrid(torch.arange(ht, device=device), torch.arange(wd, device=device), indexing="ij")
+    return torch.stack([xs, ys], dim=0).float()[None].repeat(batch, 1, 1, 1)
+
+
+class _BuildFn(torch.autograd.Function):
+    """Autograd node of the volume build.  Its output is a one-element token
+    that every lookup takes as an input, so autograd runs this backward once,
+    after all lookup backwards have accumulated into the gradient pyramid."""
+
+    @staticmethod
+    def forward(ctx, fmap1, fmap2, blk):
+        blk._build(fmap1, fmap2)
+        ctx.blk = blk
+        ctx.save_for_backward(fmap1, fmap2)
+        return torch.zeros(1, device=fmap1.device, dtype=torch.float32)
+
+    @staticmethod
+    def backward(ctx, _token_grad):
+        fmap1, fmap2 = ctx.saved_tensors
+        d1, d2 = ctx.blk._build_backward(fmap1, fmap2)
+        return d1, d2, None
+
+
+class _LookupFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, coords, token, blk):
+        ctx.blk = blk
+        ctx.save_for_backward(coords)
+        ctx.has_token = token is not None
+        return blk._lookup(coords)
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        (coords,) = ctx.saved_tensors
+        blk = ctx.blk
+        want_vol = ctx.has_token and ctx.needs_input_grad[1]
+        dcoords = blk._lookup_backward(coords, grad_out.contiguous(), want_vol, ctx.needs_input_grad[0])
+        token_grad = torch.zeros(1, device=coords.device) if want_vol else None
+        return dcoords, token_grad, None
+
+
+class CorrBlock:
+    """All-pairs correlation volume, 4-level pooled pyramid and windowed lookup.
+
+    storage: "bf16" (default) or "fp32" -- element type of the stored pyramid.
+    math:    "bf16" (default; tcgen05 tensor cores, fp32 accumulate) or "fp32"
+             (CUDA-core fp32 FMA, the reference's SGEMM arithmetic).
+    Defaults can be set with RAFT_CORR_STORAGE / RAFT_CORR_MATH.
+    """
+
+    def __init__(self, fmap1, fmap2, num_levels: int = 4, radius: int = 4, *,
+                 storage: Optional[str] = None, math: Optional[str] = None):
+        self.num_levels = num_levels
+        self.radius = radius
+        storage = storage or os.environ.get("RAFT_CORR_STORAGE", "bf16")
+        math = math or os.environ.get("RAFT_CORR_MATH", "bf16")
+        if storage not in _STORAGE or math not in _MATH:
+            raise RaftCorrError(f"storage={storage!r} math={math!r}: expected bf16|fp32")
+        self.vol_dtype = _STORAGE[storage]
+        self.math = _MATH[math]
+        _lib.lib()   # fail loudly before touching tensors if the extension is missing
+
+        f1 = _require_cuda_f32(fmap1, "fmap1")
+        f2 = _require_cuda_f32(fmap2, "fmap2")
+        if f1.shape != f2.shape or f1.dim() != 4:
+            raise RaftCorrError(f"fmap shapes {tuple(f1.shape)} vs {tuple(f2.shape)}: expected equal [B,D,H,W]")
+        if f1.device != f2.device:
+            raise RaftCorrError("fmap1 and fmap2 must be on the same device")
+        self.B, self.D, self.H, self.W = (int(v) for v in f1.shape)
+        self.device = f1.device
+        self.layout = _lib.pyramid_layout(self.B, self.H, self.W, num_levels, self.vol_dtype)
+        self._buf = None
+        self._grad_buf = None
+        self._token = None
+
+        if torch.is_grad_enabled() and (f1.requires_grad or f2.requires_grad):
+            self._token = _BuildFn.apply(f1, f2, self)
+        else:
+            self._build(f1, f2)
+
+    # ------------------------------------------------------------------ build
+    def _build(self, f1: torch.Tensor, f2: torch.Tensor) -> None:
+        L = _lib.lib()
+        lay = self.layout
+        self._buf = torch.empty(int(lay.total_elems), dtype=_TORCH_DT[self.vol_dtype], device=self.device)
+        ws_bytes = int(L.rc_build_workspace_bytes(self.B, self.D, self.H, self.W, self.math))
+        if ws_bytes < 0:
+            raise RaftCorrError("rc_build_workspace_bytes rejected the sizes")
+        ws = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=self.device)
+        with torch.cuda.device(self.device):
+            check(L.rc_build_pyramid(f1.data_ptr(), f2.data_ptr(), self.B, self.D, self.H, self.W,
+                                     self.num_levels, self.vol_dtype, self.math, self._buf.data_ptr(),
+                                     ws.data_ptr(), ws_bytes, _stream(f1)), "rc_build_pyramid")
+        ws.record_stream(torch.cuda.current_stream(self.device))
+
+    @property
+    def corr_pyramid(self) -> List[torch.Tensor]:
+        """Views [B*N, 1, H_l, W_l] over the pyramid buffer (row pitch padded)."""
+        lay = self.layout
+        views = []
+        for l in range(self.num_levels):
+            views.append(torch.as_strided(
+                self._buf, (self.B * lay.N, 1, lay.H[l], lay.W[l]),
+                (lay.slab[l], lay.slab[l], lay.pitch[l], 1), int(lay.offset[l])))
+        return views
+
+    @staticmethod
+    def corr(fmap1, fmap2):
+        """[B,H,W,1,H,W] fp32 volume, 1/sqrt(D)-scaled (core/corr.py:52-60)."""
+        blk = CorrBlock(fmap1.detach(), fmap2.detach(), num_levels=1, storage="fp32", math="fp32")
+        B, H, W = blk.B, blk.H, blk.W
+        return blk.corr_pyramid[0].reshape(B, H, W, 1, H, W)
+
+    # ----------------------------------------------------------------- lookup
+    def _check_coords(self, coords: torch.Tensor) -> torch.Tensor:
+        c = _require_cuda_f32(coords, "coords")
+        if tuple(c.shape) != (self.B, 2, self.H, self.W):
+            raise RaftCorrError(f"coords shape {tuple(c.shape)}, expected {(self.B, 2, self.H, self.W)}")
+        if c.device != self.device:
+            raise RaftCorrError("coords must be on the pyramid's device")
+        return c
+
+    def _lookup(self, coords: torch.Tensor) -> torch.Tensor:
+        n = 2 * self.radius + 1
+        out = torch.empty(self.B, self.num_levels * n * n, self.H, self.W, dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            check(_lib.lib().rc_lookup_fwd(self._buf.data_ptr(), self.vol_dtype, coords.data_ptr(), self.B,
+                                           self.H, self.W, self.num_levels, self.radius, out.data_ptr(),
+                                           _stream(coords)), "rc_lookup_fwd")
+        return out
+
+    def __call__(self, coords: torch.Tensor) -> torch.Tensor:
+        c = self._check_coords(coords)
+        if torch.is_grad_enabled() and (self._token is not None or c.requires_grad):
+            return _LookupFn.apply(c, self._token, self)
+        return self._lookup(c)
+
+    # --------------------------------------------------------------- backward
+    def _lookup_backward(self, coords, grad_out, want_vol: bool, want_coords: bool):
+        L = _lib.lib()
+        if want_vol and self._grad_buf is None:
+            glay = _lib.pyramid_layout(self.B, self.H, self.W, self.num_levels, _lib.RC_VOL_F32)
+            self._grad_buf = torch.zeros(int(glay.total_elems), dtype=torch.float32, device=self.device)
+        dcoords = torch.empty_like(coords) if want_coords else None
+        if not (want_vol or want_coords):
+            return None
+        with torch.cuda.device(self.device):
+            check(L.rc_lookup_bwd(self._buf.data_ptr(), self.vol_dtype, coords.data_ptr(), grad_out.data_ptr(),
+                                  self.B, self.H, self.W, self.num_levels, self.radius,
+                                  self._grad_buf.data_ptr() if want_vol else None,
+                                  dcoords.data_ptr() if want_coords else None, _stream(coords)),
+                  "rc_lookup_bwd")
+        return dcoords
+
+    def _build_backward(self, f1, f2):
+        d1 = torch.empty_like(f1)
+        d2 = torch.empty_like(f2)
+        if self._grad_buf is None:   # no lookup contributed
+            return d1.zero_(), d2.zero_()
+        L = _lib.lib()
+        ws_bytes = int(L.rc_build_bwd_workspace_bytes(self.B, self.D, self.H, self.W, self.num_levels))
+        ws = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=self.device)
+        with torch.cuda.device(self.device):
+            check(L.rc_build_bwd(self._grad_buf.data_ptr(), f1.data_ptr(), f2.data_ptr(), self.B, self.D,
+                                 self.H, self.W, self.num_levels, d1.data_ptr(), d2.data_ptr(),
+                                 ws.data_ptr(), ws_bytes, _stream(f1)), "rc_build_bwd")
+        ws.record_stream(torch.cuda.current_stream(self.device))
+        self._grad_buf.record_stream(torch.cuda.current_stream(self.device))
+        self._grad_buf = None
+        return d1, d2
+
+
+class AlternateCorrBlock:
+    """Memory-lean variant: feature dot products fused with the bilinear taps,
+    the volume is never built (reference: core/corr.py:63-91 calling
+    alt_cuda_corr.forward once per level; here one launch covers all levels).
+    Like the reference, the output carries no autograd history."""
+
+    def __init__(self, fmap1, fmap2, num_levels: int = 4, radius: int = 4):
+        self.num_levels = num_levels
+        self.radius = radius
+        L = _lib.lib()
+        f1 = _require_cuda_f32(fmap1.detach(), "fmap1")
+        f2 = _require_cuda_f32(fmap2.detach(), "fmap2")
+        if f1.shape != f2.shape or f1.dim() != 4:
+            raise RaftCorrError(f"fmap shapes {tuple(f1.shape)} vs {tuple(f2.shape)}: expected equal [B,D,H,W]")
+        self.B, self.D, self.H, self.W = (int(v) for v in f1.shape)
+        self.device = f1.device
+        offs = (C.c_int64 * _lib.RC_MAX_LEVELS)()
+        total = int(L.rc_alt_feature_pyramid_elems(self.B, self.D, self.H, self.W, num_levels, offs))
+        if total <= 0:
+            raise RaftCorrError("rc_alt_feature_pyramid_elems rejected the sizes")
+        self._offs = [int(offs[l]) for l in range(num_levels)]
+        self._f1 = torch.empty(self.B, self.H, self.W, self.D, dtype=torch.float32, device=self.device)
+        self._f2 = torch.empty(total, dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            check(L.rc_alt_pool_features(f1.data_ptr(), f2.data_ptr(), self.B, self.D, self.H, self.W,
+                                         num_levels, self._f1.data_ptr(), self._f2.data_ptr(), _stream(f1)),
+                  "rc_alt_pool_features")
+        # same attribute as the reference: [(fmap1, fmap2), pooled levels ...] as NCHW views
+        self.pyramid = [(fmap1, fmap2)]
+        for l in range(1, num_levels):
+            h, w = self.H >> l, self.W >> l
+            v = self._f2[self._offs[l]: self._offs[l] + self.B * h * w * self.D].view(self.B, h, w, self.D)
+            self.pyramid.append((None, v.permute(0, 3, 1, 2)))
+
+    def __call__(self, coords: torch.Tensor) -> torch.Tensor:
+        c = _require_cuda_f32(coords.detach(), "coords")
+        if tuple(c.shape) != (self.B, 2, self.H, self.W):
+            raise RaftCorrError(f"coords shape {tuple(c.shape)}, expected {(self.B, 2, self.H, self.W)}")
+        n = 2 * self.radius + 1
+        out = torch.empty(self.B, self.num_levels * n * n, self.H, self.W, dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            check(_lib.lib().rc_alt_lookup_fwd(self._f1.data_ptr(), self._f2.data_ptr(), c.data_ptr(), self.B,
+                                               self.D, self.H, self.W, self.num_levels, self.radius,
+                                               out.data_ptr(), _stream(c)), "rc_alt_lookup_fwd")
+        return out
+
+
+def install_into(raft_module) -> None:
+    """Swap the two names `core/raft.py:8` imports, e.g. install_into(sys.modules['raft'])."""
+    raft_module.CorrBlock = CorrBlock
+    raft_module.AlternateCorrBlock = AlternateCorrBlock

@@ -1,0 +1,224 @@
+// extern "C" entry points of libraftcorr (declared in include/raft_corr.h).
+// Argument validation, layout arithmetic and dispatch only; kernels live in the
+// other translation units.
+#include <math.h>
+#include <stdarg.h>
+#include <string.h>
+
+#include "common.cuh"
+
+namespace rc {
+
+static thread_local char g_error[512] = "";
+
+void set_error(const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_error, sizeof(g_error), fmt, ap);
+  va_end(ap);
+}
+
+// alt.cu
+int launch_alt_fwd(const float *fmap1, const float *fmap2, const float *coords, int B, int H1, int W1,
+                   int H2, int W2, int C, int Nc, int radius, float *corr, cudaStream_t s);
+int launch_alt_lookup_fwd(const float *fmap1_nhwc, const float *fmap2_pyr, const float *coords, int B,
+                          int D, int H, int W, int num_levels, int radius, const int64_t *off,
+                          float *out, cudaStream_t s);
+int launch_alt_bwd(const float *fmap1, const float *fmap2, const float *coords, const float *corr_grad,
+                   int B, int H1, int W1, int H2, int W2, int C, int Nc, int radius, float *g1,
+                   float *g2, cudaStream_t s);
+int launch_alt_pool(const float *fmap1, const float *fmap2, int B, int D, int H, int W, int num_levels,
+                    const int64_t *off, float *f1_nhwc, float *f2_pyr, cudaStream_t s);
+// build_bwd.cu
+int64_t build_bwd_workspace_bytes(int B, int D, int H, int W, int num_levels);
+int launch_build_bwd(const float *grad_pyramid, const float *fmap1, const float *fmap2, int B, int D,
+                     int H, int W, const rc_layout &glay, float *dfmap1, float *dfmap2, void *workspace,
+                     size_t workspace_bytes, cudaStream_t s);
+
+static int make_layout(int B, int H, int W, int num_levels, int vol_dtype, rc_layout *out) {
+  RC_REQUIRE(out != nullptr, "rc_pyramid_layout: out is NULL");
+  RC_REQUIRE(B >= 1 && H >= 1 && W >= 1, "rc_pyramid_layout: bad sizes B=%d H=%d W=%d", B, H, W);
+  RC_REQUIRE(num_levels >= 1 && num_levels <= RC_MAX_LEVELS, "num_levels %d outside 1..%d", num_levels,
+             RC_MAX_LEVELS);
+  RC_REQUIRE(vol_dtype == RC_VOL_F32 || vol_dtype == RC_VOL_BF16, "unknown vol_dtype %d", vol_dtype);
+  RC_REQUIRE((H >> (num_levels - 1)) >= 1 && (W >> (num_levels - 1)) >= 1,
+             "a %dx%d map has no level %d (avg_pool2d would produce an empty tensor)", H, W,
+             num_levels - 1);
+  RC_REQUIRE((long long)H * W < (1ll << 31) / 64, "feature map too large");
+  memset(out, 0, sizeof(*out));
+  out->num_levels = num_levels;
+  out->B = B;
+  out->N = H * W;
+  out->elem_bytes = vol_dtype == RC_VOL_BF16 ? 2 : 4;
+  // rows start on 32-byte sectors: 16 bf16 or 8 fp32 elements
+  const int align = 32 / out->elem_bytes;
+  int64_t off = 0;
+  for (int l = 0; l < num_levels; ++l) {
+    out->H[l] = H >> l;
+    out->W[l] = W >> l;
+    out->pitch[l] = (int)round_up64(out->W[l], align);
+    out->slab[l] = (int64_t)out->H[l] * out->pitch[l];
+    out->offset[l] = off;
+    off += round_up64((int64_t)B * out->N * out->slab[l], 256);
+  }
+  out->total_elems = off;
+  return RC_OK;
+}
+
+static int64_t packed_rows2(int H, int W) {
+  return (int64_t)ceil_div(W, TB_W) * ceil_div(H, TB_H) * TB_N;
+}
+
+}  // namespace rc
+
+using namespace rc;
+
+extern "C" {
+
+int rc_abi_version(void) { return RC_ABI_VERSION; }
+
+const char *rc_last_error(void) { return g_error; }
+
+int rc_pyramid_layout(int B, int H, int W, int num_levels, int vol_dtype, rc_layout *out) {
+  return make_layout(B, H, W, num_levels, vol_dtype, out);
+}
+
+int64_t rc_build_workspace_bytes(int B, int D, int H, int W, int math) {
+  if (math == RC_MATH_F32) return 0;
+  if (B < 1 || D < 1 || H < 1 || W < 1) return RC_EINVAL;
+  const int64_t es = math == RC_MATH_BF16 ? 2 : 4;
+  const int64_t a = round_up64((int64_t)B * H * W * D * es, 1024);
+  const int64_t b = round_up64((int64_t)B * packed_rows2(H, W) * D * es, 1024);
+  return a + b;
+}
+
+int rc_build_pyramid(const float *fmap1, const float *fmap2, int B, int D, int H, int W, int num_levels,
+                     int vol_dtype, int math, void *pyramid, void *workspace, size_t workspace_bytes,
+                     rc_stream_t stream) {
+  RC_REQUIRE(fmap1 && fmap2 && pyramid, "rc_build_pyramid: NULL pointer");
+  RC_REQUIRE(D >= 1, "rc_build_pyramid: D=%d", D);
+  RC_REQUIRE(math == RC_MATH_F32 || math == RC_MATH_BF16 || math == RC_MATH_TF32, "unknown math %d", math);
+  rc_layout lay;
+  int r = make_layout(B, H, W, num_levels, vol_dtype, &lay);
+  if (r) return r;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (math == RC_MATH_F32) return launch_build_simt(fmap1, fmap2, B, D, H, W, lay, vol_dtype, pyramid, s);
+  RC_REQUIRE(math == RC_MATH_BF16, "RC_MATH_TF32 is declared but not built in this version");
+  const int64_t need = rc_build_workspace_bytes(B, D, H, W, math);
+  if (workspace == nullptr || (int64_t)workspace_bytes < need) {
+    set_error("rc_build_pyramid: workspace of %zu bytes, need %lld", workspace_bytes, (long long)need);
+    return RC_ESIZE;
+  }
+  RC_REQUIRE(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
+  RC_REQUIRE(((uintptr_t)pyramid & 255) == 0, "pyramid must be 256-byte aligned");
+  const int64_t es = 2;
+  void *f1p = workspace;
+  void *f2p = (char *)workspace + round_up64((int64_t)B * H * W * D * es, 1024);
+  r = launch_pack(fmap1, fmap2, B, D, H, W, math, f1p, f2p, s);
+  if (r) return r;
+  return launch_build_tc(f1p, f2p, B, D, H, W, lay, vol_dtype, math, pyramid, s);
+}
+
+int rc_lookup_fwd(const void *pyramid, int vol_dtype, const float *coords, int B, int H, int W,
+                  int num_levels, int radius, float *out, rc_stream_t stream) {
+  RC_REQUIRE(pyramid && coords && out, "rc_lookup_fwd: NULL pointer");
+  RC_REQUIRE(radius >= 1 && radius <= 4, "radius %d unsupported (1..4)", radius);
+  rc_layout lay;
+  int r = make_layout(B, H, W, num_levels, vol_dtype, &lay);
+  if (r) return r;
+  return launch_lookup_fwd(pyramid, vol_dtype, coords, lay, H, W, radius, out, (cudaStream_t)stream);
+}
+
+int rc_lookup_bwd(const void *pyramid, int vol_dtype, const float *coords, const float *grad_out, int B,
+                  int H, int W, int num_levels, int radius, float *grad_pyramid, float *grad_coords,
+                  rc_stream_t stream) {
+  RC_REQUIRE(coords && grad_out, "rc_lookup_bwd: NULL pointer");
+  RC_REQUIRE(grad_pyramid || grad_coords, "rc_lookup_bwd: nothing to compute");
+  RC_REQUIRE(!grad_coords || pyramid, "rc_lookup_bwd: grad_coords needs the pyramid");
+  RC_REQUIRE(radius >= 1 && radius <= 4, "radius %d unsupported (1..4)", radius);
+  rc_layout lay, glay;
+  int r = make_layout(B, H, W, num_levels, vol_dtype, &lay);
+  if (r) return r;
+  r = make_layout(B, H, W, num_levels, RC_VOL_F32, &glay);
+  if (r) return r;
+  return launch_lookup_bwd(pyramid, vol_dtype, coords, grad_out, lay, glay, H, W, radius, grad_pyramid,
+                           grad_coords, (cudaStream_t)stream);
+}
+
+int64_t rc_build_bwd_workspace_bytes(int B, int D, int H, int W, int num_levels) {
+  return build_bwd_workspace_bytes(B, D, H, W, num_levels);
+}
+
+int rc_build_bwd(const float *grad_pyramid, const float *fmap1, const float *fmap2, int B, int D, int H,
+                 int W, int num_levels, float *dfmap1, float *dfmap2, void *workspace,
+                 size_t workspace_bytes, rc_stream_t stream) {
+  RC_REQUIRE(grad_pyramid && fmap1 && fmap2 && dfmap1 && dfmap2, "rc_build_bwd: NULL pointer");
+  rc_layout glay;
+  int r = make_layout(B, H, W, num_levels, RC_VOL_F32, &glay);
+  if (r) return r;
+  const int64_t need = build_bwd_workspace_bytes(B, D, H, W, num_levels);
+  if (need > 0 && (workspace == nullptr || (int64_t)workspace_bytes < need)) {
+    set_error("rc_build_bwd: workspace of %zu bytes, need %lld", workspace_bytes, (long long)need);
+    return RC_ESIZE;
+  }
+  return launch_build_bwd(grad_pyramid, fmap1, fmap2, B, D, H, W, glay, dfmap1, dfmap2, workspace,
+                          workspace_bytes, (cudaStream_t)stream);
+}
+
+int rc_alt_fwd(const float *fmap1, const float *fmap2, const float *coords, int B, int H1, int W1, int H2,
+               int W2, int C, int Nc, int radius, float *corr, rc_stream_t stream) {
+  RC_REQUIRE(fmap1 && fmap2 && coords && corr, "rc_alt_fwd: NULL pointer");
+  RC_REQUIRE(B >= 1 && H1 >= 1 && W1 >= 1 && H2 >= 1 && W2 >= 1 && Nc >= 1, "rc_alt_fwd: bad sizes");
+  RC_REQUIRE(C >= 4 && C % 4 == 0 && C <= 512, "rc_alt_fwd: C=%d must be a multiple of 4, at most 512", C);
+  RC_REQUIRE(radius >= 1 && radius <= 4, "radius %d unsupported (1..4)", radius);
+  RC_REQUIRE(Nc <= RC_MAX_LEVELS, "rc_alt_fwd: at most %d coordinate sets per call (got %d)",
+             RC_MAX_LEVELS, Nc);
+  return launch_alt_fwd(fmap1, fmap2, coords, B, H1, W1, H2, W2, C, Nc, radius, corr, (cudaStream_t)stream);
+}
+
+int rc_alt_bwd(const float *fmap1, const float *fmap2, const float *coords, const float *corr_grad, int B,
+               int H1, int W1, int H2, int W2, int C, int Nc, int radius, float *fmap1_grad,
+               float *fmap2_grad, float *coords_grad, rc_stream_t stream) {
+  RC_REQUIRE(fmap1 && fmap2 && coords && corr_grad && fmap1_grad && fmap2_grad, "rc_alt_bwd: NULL pointer");
+  RC_REQUIRE(B >= 1 && H1 >= 1 && W1 >= 1 && H2 >= 1 && W2 >= 1 && Nc >= 1, "rc_alt_bwd: bad sizes");
+  RC_REQUIRE(C >= 4 && C % 4 == 0 && C <= 512, "rc_alt_bwd: C=%d must be a multiple of 4, at most 512", C);
+  RC_REQUIRE(radius >= 1 && radius <= 4, "radius %d unsupported (1..4)", radius);
+  cudaStream_t s = (cudaStream_t)stream;
+  RC_CUDA(cudaMemsetAsync(fmap2_grad, 0, (size_t)B * H2 * W2 * C * sizeof(float), s));
+  if (coords_grad) RC_CUDA(cudaMemsetAsync(coords_grad, 0, (size_t)B * Nc * H1 * W1 * 2 * sizeof(float), s));
+  return launch_alt_bwd(fmap1, fmap2, coords, corr_grad, B, H1, W1, H2, W2, C, Nc, radius, fmap1_grad,
+                        fmap2_grad, s);
+}
+
+int64_t rc_alt_feature_pyramid_elems(int B, int D, int H, int W, int num_levels, int64_t *f2_offset) {
+  if (B < 1 || D < 1 || H < 1 || W < 1 || num_levels < 1 || num_levels > RC_MAX_LEVELS) return RC_EINVAL;
+  int64_t off = 0;
+  for (int l = 0; l < num_levels; ++l) {
+    if (f2_offset) f2_offset[l] = off;
+    off += round_up64((int64_t)B * (H >> l) * (W >> l) * D, 64);
+  }
+  return off;
+}
+
+int rc_alt_pool_features(const float *fmap1, const float *fmap2, int B, int D, int H, int W, int num_levels,
+                         float *fmap1_nhwc, float *fmap2_pyr, rc_stream_t stream) {
+  RC_REQUIRE(fmap1 && fmap2 && fmap1_nhwc && fmap2_pyr, "rc_alt_pool_features: NULL pointer");
+  RC_REQUIRE(D >= 4 && D % 4 == 0, "rc_alt_pool_features: D=%d must be a multiple of 4", D);
+  int64_t off[RC_MAX_LEVELS];
+  RC_REQUIRE(rc_alt_feature_pyramid_elems(B, D, H, W, num_levels, off) > 0, "rc_alt_pool_features: bad sizes");
+  return launch_alt_pool(fmap1, fmap2, B, D, H, W, num_levels, off, fmap1_nhwc, fmap2_pyr, (cudaStream_t)stream);
+}
+
+int rc_alt_lookup_fwd(const float *fmap1_nhwc, const float *fmap2_pyr, const float *coords, int B, int D,
+                      int H, int W, int num_levels, int radius, float *out, rc_stream_t stream) {
+  RC_REQUIRE(fmap1_nhwc && fmap2_pyr && coords && out, "rc_alt_lookup_fwd: NULL pointer");
+  RC_REQUIRE(D >= 4 && D % 4 == 0 && D <= 512, "rc_alt_lookup_fwd: D=%d must be a multiple of 4, at most 512", D);
+  RC_REQUIRE(radius >= 1 && radius <= 4, "radius %d unsupported (1..4)", radius);
+  int64_t off[RC_MAX_LEVELS];
+  RC_REQUIRE(rc_alt_feature_pyramid_elems(B, D, H, W, num_levels, off) > 0, "rc_alt_lookup_fwd: bad sizes");
+  RC_REQUIRE((H >> (num_levels - 1)) >= 1 && (W >> (num_levels - 1)) >= 1, "map too small for %d levels", num_levels);
+  return launch_alt_lookup_fwd(fmap1_nhwc, fmap2_pyr, coords, B, D, H, W, num_levels, radius, off, out,
+                               (cudaStream_t)stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,97 @@
+// Shared declarations for libraftcorr's translation units (sm_100a only).
+#pragma once
+
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/raft_corr.h"
+
+namespace rc {
+
+// ---- error reporting -------------------------------------------------------
+void set_error(const char *fmt, ...);   // api.cu; thread-local message
+
+#define RC_REQUIRE(cond, ...)            \
+  do {                                   \
+    if (!(cond)) {                       \
+      rc::set_error(__VA_ARGS__);        \
+      return RC_EINVAL;                  \
+    }                                    \
+  } while (0)
+
+#define RC_CUDA(call)                                                              \
+  do {                                                                             \
+    cudaError_t e__ = (call);                                                      \
+    if (e__ != cudaSuccess) {                                                      \
+      rc::set_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__),       \
+                    __FILE__, __LINE__);                                           \
+      return RC_ECUDA;                                                             \
+    }                                                                              \
+  } while (0)
+
+#define RC_LAUNCH_CHECK(name)                                                      \
+  do {                                                                             \
+    cudaError_t e__ = cudaGetLastError();                                          \
+    if (e__ != cudaSuccess) {                                                      \
+      rc::set_error("launch of %s failed: %s", name, cudaGetErrorString(e__));     \
+      return RC_ECUDA;                                                             \
+    }                                                                              \
+  } while (0)
+
+// ---- small helpers ---------------------------------------------------------
+__host__ __device__ inline int64_t round_up64(int64_t v, int64_t m) { return (v + m - 1) / m * m; }
+__host__ __device__ inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+
+// Device-side copy of the layout: passed by value to kernels.
+struct Levels {
+  int num_levels;
+  int H[RC_MAX_LEVELS];
+  int W[RC_MAX_LEVELS];
+  int pitch[RC_MAX_LEVELS];
+  long long slab[RC_MAX_LEVELS];
+  long long offset[RC_MAX_LEVELS];
+};
+
+inline Levels to_levels(const rc_layout &lay) {
+  Levels lv{};
+  lv.num_levels = lay.num_levels;
+  for (int l = 0; l < lay.num_levels; ++l) {
+    lv.H[l] = lay.H[l];
+    lv.W[l] = lay.W[l];
+    lv.pitch[l] = lay.pitch[l];
+    lv.slab[l] = lay.slab[l];
+    lv.offset[l] = lay.offset[l];
+  }
+  return lv;
+}
+
+// Geometry of the target (fmap2) blocking used by the tensor-core build:
+// targets are grouped in spatial blocks of TB_H rows x TB_W columns so that one
+// GEMM N-tile (256 columns) is one block and the 2x2/4x4/8x8 pooling of the
+// pyramid stays inside a tile.
+constexpr int TB_H = 8;
+constexpr int TB_W = 32;
+constexpr int TB_N = TB_H * TB_W;   // 256 targets per block
+
+// ---- launchers implemented in the kernel files ----------------------------
+// pack.cu
+int launch_pack(const float *fmap1, const float *fmap2, int B, int D, int H, int W, int math,
+                void *f1p, void *f2p, cudaStream_t s);
+// build_simt.cu
+int launch_build_simt(const float *fmap1, const float *fmap2, int B, int D, int H, int W,
+                      const rc_layout &lay, int vol_dtype, void *pyramid, cudaStream_t s);
+int launch_pool_levels(const rc_layout &lay, int vol_dtype, void *pyramid, int first_level,
+                       cudaStream_t s);
+// build_tc.cu
+int launch_build_tc(const void *f1p, const void *f2p, int B, int D, int H, int W,
+                    const rc_layout &lay, int vol_dtype, int math, void *pyramid, cudaStream_t s);
+// lookup.cu
+int launch_lookup_fwd(const void *pyramid, int vol_dtype, const float *coords, const rc_layout &lay,
+                      int H, int W, int radius, float *out, cudaStream_t s);
+int launch_lookup_bwd(const void *pyramid, int vol_dtype, const float *coords, const float *grad_out,
+                      const rc_layout &lay, const rc_layout &glay, int H, int W, int radius,
+                      float *grad_pyramid, float *grad_coords, cudaStream_t s);
+
+}  // namespace rc

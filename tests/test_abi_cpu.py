@@ -1,0 +1,77 @@
+"""CPU-side checks of the boundary: the shared library loads, exports every
+symbol include/raft_corr.h declares, its host-only entry points work, and the
+Python drop-in refuses to run without a GPU (no fallback)."""
+import ctypes as C
+import os
+import re
+
+import pytest
+import torch
+
+from raft_stir_b200 import _lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    text = open(os.path.join(ROOT, "include", "raft_corr.h")).read()
+    return sorted(set(re.findall(r"RC_API[^;]*?\b(rc_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    names = declared_symbols()
+    assert len(names) >= 14
+    handle = C.CDLL(_lib.LIB_PATH)
+    for n in names:
+        assert hasattr(handle, n), f"{n} declared in raft_corr.h but not exported"
+    assert set(names) == set(_lib.SIGNATURES), "ctypes binding and header disagree"
+
+
+def test_abi_version_and_layout():
+    L = _lib.lib()
+    assert L.rc_abi_version() == _lib.RC_ABI_VERSION
+    lay = _lib.pyramid_layout(1, 55, 128, 4, _lib.RC_VOL_BF16)
+    assert list(lay.H)[:4] == [55, 27, 13, 6] and list(lay.W)[:4] == [128, 64, 32, 16]
+    assert lay.N == 7040 and lay.elem_bytes == 2
+    # 65 331 200 pyramid elements per Sintel pair (no padding needed at this shape)
+    assert lay.total_elems == 65331200
+    lay = _lib.pyramid_layout(10, 46, 62, 4, _lib.RC_VOL_F32)
+    assert list(lay.W)[:4] == [62, 31, 15, 7] and list(lay.pitch)[:4] == [64, 32, 16, 8]
+    for l in range(4):
+        assert lay.slab[l] == lay.H[l] * lay.pitch[l] and lay.offset[l] % 64 == 0
+
+
+def test_layout_rejects_bad_arguments():
+    with pytest.raises(RuntimeError, match="no level"):
+        _lib.pyramid_layout(1, 8, 8, 5, 0)     # the reference would divide by zero / pool to nothing
+    with pytest.raises(RuntimeError):
+        _lib.pyramid_layout(1, 16, 16, 7, 0)
+    with pytest.raises(RuntimeError):
+        _lib.pyramid_layout(1, 16, 16, 4, 9)
+
+
+def test_workspace_sizes():
+    L = _lib.lib()
+    assert L.rc_build_workspace_bytes(1, 256, 55, 128, _lib.RC_MATH_F32) == 0
+    # bf16 repack: N*D*2 for fmap1 + 28 blocks * 256 rows * D * 2 for fmap2
+    assert L.rc_build_workspace_bytes(1, 256, 55, 128, _lib.RC_MATH_BF16) == 7040 * 256 * 2 + 28 * 256 * 256 * 2
+    assert L.rc_build_bwd_workspace_bytes(1, 256, 55, 128, 4) > 0
+
+
+def test_no_cpu_fallback():
+    import raft_stir_b200 as R
+    with pytest.raises(RuntimeError, match="CUDA"):
+        R.CorrBlock(torch.zeros(1, 8, 16, 16), torch.zeros(1, 8, 16, 16))
+    with pytest.raises(RuntimeError, match="CUDA"):
+        R.AlternateCorrBlock(torch.zeros(1, 8, 16, 16), torch.zeros(1, 8, 16, 16))
+    with pytest.raises(RuntimeError, match="CUDA"):
+        R.alt_cuda_corr.forward(torch.zeros(1, 4, 4, 8), torch.zeros(1, 4, 4, 8), torch.zeros(1, 1, 4, 4, 2), 4)
+
+
+def test_product_does_not_import_oracle():
+    pkg = os.path.join(ROOT, "raft_stir_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert "oracle" not in src, f"{f} mentions the oracle"

@@ -1,0 +1,321 @@
+"""GPU parity tests: the CUDA path (through the C ABI, via the ctypes binding)
+against the CPU oracle and the fixtures frozen from the reference's CorrBlock.
+
+Tolerances (BASELINE.json north_star): correlation values within 1e-2 relative
+for bf16, 1e-4 for fp32; written next to each assert.
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import corr_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+R = pytest.importorskip("raft_stir_b200")
+
+
+def dev():
+    if not torch.cuda.is_available():
+        pytest.fail("GPU test selected but torch.cuda.is_available() is False")
+    return torch.device("cuda:0")
+
+
+def t(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(dev())
+
+
+def bf16_round(a):
+    return torch.from_numpy(a).to(torch.bfloat16).float().numpy()
+
+
+def rel_close(got, ref, rel, what):
+    """|got-ref| <= rel * (|ref| + rms(ref)): relative to the value, with the
+    volume's rms as the floor for entries that are near zero."""
+    got = np.asarray(got, np.float64)
+    ref = np.asarray(ref, np.float64)
+    assert got.shape == ref.shape, (what, got.shape, ref.shape)
+    rms = float(np.sqrt(np.mean(ref ** 2))) + 1e-30
+    err = np.abs(got - ref)
+    bound = rel * (np.abs(ref) + rms)
+    bad = err > bound
+    assert not bad.any(), f"{what}: {bad.sum()} / {bad.size} outside {rel:g} rel; max err {err.max():.3e}, rms {rms:.3e}"
+
+
+KINDS = ["rand", "int", "far", "edge"]
+
+
+# ------------------------------------------------------------------ build
+def test_build_fp32_matches_reference(golden):
+    blk = R.CorrBlock(t(golden["fmap1"]), t(golden["fmap2"]), 4, int(golden["radius"]), storage="fp32", math="fp32")
+    for l, v in enumerate(blk.corr_pyramid):
+        assert v.shape[1] == 1
+        rel_close(v[:, 0].cpu().numpy(), golden[f"pyr{l}"], 1e-4, f"fp32 level {l}")   # 1e-4 (fp32)
+
+
+@pytest.mark.parametrize("storage", ["bf16", "fp32"])
+def test_build_tensor_core_matches_reference(golden, storage):
+    blk = R.CorrBlock(t(golden["fmap1"]), t(golden["fmap2"]), 4, int(golden["radius"]), storage=storage, math="bf16")
+    # (a) against the reference's fp32 values: 1e-2 relative (bf16)
+    for l, v in enumerate(blk.corr_pyramid):
+        rel_close(v[:, 0].float().cpu().numpy(), golden[f"pyr{l}"], 1e-2, f"bf16/{storage} level {l}")
+    # (b) against the oracle fed the same bf16-rounded features: only storage rounding remains
+    pyr = O.corr_pyramid(bf16_round(golden["fmap1"]).astype(np.float64), bf16_round(golden["fmap2"]).astype(np.float64), 4)
+    tol = 2.0 ** -8 if storage == "bf16" else 1e-5
+    for l, v in enumerate(blk.corr_pyramid):
+        rel_close(v[:, 0].float().cpu().numpy(), pyr[l], tol, f"bf16-exact/{storage} level {l}")
+
+
+@pytest.mark.parametrize("shape", [(1, 256, 55, 128), (2, 128, 46, 62), (1, 64, 17, 33), (3, 32, 8, 9)])
+@pytest.mark.parametrize("storage", ["bf16", "fp32"])
+def test_build_tensor_core_vs_oracle_shapes(shape, storage):
+    B, D, H, W = shape
+    rng = np.random.default_rng(H * W + D)
+    f1 = rng.standard_normal(shape).astype(np.float32)
+    f2 = rng.standard_normal(shape).astype(np.float32)
+    L = 4 if min(H, W) >= 8 else 3
+    blk = R.CorrBlock(t(f1), t(f2), L, 4, storage=storage, math="bf16")
+    pyr = O.corr_pyramid(bf16_round(f1), bf16_round(f2), L)
+    tol = 2.0 ** -8 if storage == "bf16" else 2e-5
+    for l, v in enumerate(blk.corr_pyramid):
+        rel_close(v[:, 0].float().cpu().numpy(), pyr[l], tol, f"shape {shape} {storage} level {l}")
+    # 1e-2 relative against the unrounded fp32 oracle as well
+    ref = O.corr_pyramid(f1, f2, L)
+    for l, v in enumerate(blk.corr_pyramid):
+        rel_close(v[:, 0].float().cpu().numpy(), ref[l], 1e-2, f"shape {shape} {storage} level {l} vs fp32")
+
+
+def test_build_fp32_vs_oracle_ragged():
+    rng = np.random.default_rng(5)
+    f1 = rng.standard_normal((2, 24, 19, 23)).astype(np.float32)
+    f2 = rng.standard_normal((2, 24, 19, 23)).astype(np.float32)
+    blk = R.CorrBlock(t(f1), t(f2), 4, 3, storage="fp32", math="fp32")
+    for l, (v, ref) in enumerate(zip(blk.corr_pyramid, O.corr_pyramid(f1, f2, 4))):
+        rel_close(v[:, 0].cpu().numpy(), ref, 1e-4, f"ragged level {l}")
+
+
+def test_corr_staticmethod_shape_and_values(golden):
+    vol = R.CorrBlock.corr(t(golden["fmap1"]), t(golden["fmap2"]))
+    B, D, H, W = golden["fmap1"].shape
+    assert tuple(vol.shape) == (B, H, W, 1, H, W)
+    rel_close(vol.reshape(B * H * W, H, W).cpu().numpy(), golden["pyr0"], 1e-4, "CorrBlock.corr")
+
+
+# ------------------------------------------------------------------ lookup
+@pytest.mark.parametrize("kind", KINDS)
+def test_lookup_fp32_matches_reference(golden, kind):
+    blk = R.CorrBlock(t(golden["fmap1"]), t(golden["fmap2"]), 4, int(golden["radius"]), storage="fp32", math="fp32")
+    out = blk(t(golden[f"coords_{kind}"]))
+    ref = golden[f"out_{kind}"]
+    assert out.dtype == torch.float32 and out.is_contiguous() and tuple(out.shape) == ref.shape
+    rel_close(out.cpu().numpy(), ref, 1e-4, f"lookup fp32 {kind}")   # 1e-4 (fp32)
+    if kind == "far":
+        assert not out.any().item()
+
+
+@pytest.mark.parametrize("kind", KINDS)
+def test_lookup_bf16_matches_reference(golden, kind):
+    blk = R.CorrBlock(t(golden["fmap1"]), t(golden["fmap2"]), 4, int(golden["radius"]))   # defaults: bf16/bf16
+    out = blk(t(golden[f"coords_{kind}"]))
+    rel_close(out.cpu().numpy(), golden[f"out_{kind}"], 1e-2, f"lookup bf16 {kind}")   # 1e-2 (bf16)
+
+
+@pytest.mark.parametrize("radius", [1, 2, 3, 4])
+@pytest.mark.parametrize("storage", ["bf16", "fp32"])
+def test_lookup_isolated_from_build(radius, storage):
+    """Lookup alone: pyramid values written by torch into the library's layout,
+    compared with the oracle's lookup on exactly those values."""
+    from raft_stir_b200 import _lib
+    B, H, W, L = 2, 21, 37, 4
+    rng = np.random.default_rng(radius)
+    blk = R.CorrBlock(t(np.zeros((B, 8, H, W), np.float32)), t(np.zeros((B, 8, H, W), np.float32)), L, radius,
+                      storage=storage, math="fp32")
+    pyr = []
+    for l, v in enumerate(blk.corr_pyramid):
+        vals = torch.from_numpy(rng.standard_normal(tuple(v.shape)).astype(np.float32)).to(v.dtype)
+        v.copy_(vals.to(dev()))
+        pyr.append(vals.float().numpy()[:, 0])
+    coords = (O.coords_grid(B, H, W) + rng.normal(0, 6, (B, 2, H, W))).astype(np.float32)
+    out = blk(t(coords)).cpu().numpy()
+    rel_close(out, O.window_lookup(pyr, coords, radius), 2e-5, f"isolated lookup r={radius} {storage}")
+
+
+def test_lookup_far_and_nonfinite_coords_are_zero():
+    B, H, W = 1, 16, 24
+    rng = np.random.default_rng(0)
+    blk = R.CorrBlock(t(rng.standard_normal((B, 16, H, W)).astype(np.float32)),
+                      t(rng.standard_normal((B, 16, H, W)).astype(np.float32)), 4, 4)
+    c = torch.full((B, 2, H, W), 3.0e9, device=dev())
+    assert not blk(c).any().item()
+    c = torch.full((B, 2, H, W), float("inf"), device=dev())
+    assert not blk(c).any().item()
+    c = torch.full((B, 2, H, W), -1.0e4, device=dev())
+    assert not blk(c).any().item()
+
+
+# ------------------------------------------------------------------ backward
+def test_backward_matches_reference_autograd(golden):
+    f1 = t(golden["fmap1"]).requires_grad_(True)
+    f2 = t(golden["fmap2"]).requires_grad_(True)
+    c = t(golden["coords_rand"]).requires_grad_(True)
+    blk = R.CorrBlock(f1, f2, 4, int(golden["radius"]), storage="fp32", math="fp32")
+    out = blk(c)
+    rel_close(out.detach().cpu().numpy(), golden["out_rand"], 1e-4, "fwd under autograd")
+    out.backward(t(golden["grad_out"]))
+    rel_close(c.grad.cpu().numpy(), golden["dcoords"], 2e-3, "dcoords")
+    rel_close(f1.grad.cpu().numpy(), golden["dfmap1"], 1e-3, "dfmap1")
+    rel_close(f2.grad.cpu().numpy(), golden["dfmap2"], 1e-3, "dfmap2")
+
+
+def test_lookup_backward_grad_pyramid(golden):
+    """d/dpyramid of the lookup alone (levels as leaves in the reference)."""
+    import ctypes as C
+    from raft_stir_b200 import _lib
+    r = int(golden["radius"])
+    blk = R.CorrBlock(t(golden["fmap1"]), t(golden["fmap2"]), 4, r, storage="fp32", math="fp32")
+    B, H, W = blk.B, blk.H, blk.W
+    glay = _lib.pyramid_layout(B, H, W, 4, _lib.RC_VOL_F32)
+    gbuf = torch.zeros(int(glay.total_elems), device=dev())
+    coords = t(golden["coords_rand"])
+    go = t(golden["grad_out"])
+    for rep in range(2):   # accumulates: two calls give twice the gradient
+        _lib.check(_lib.lib().rc_lookup_bwd(blk._buf.data_ptr(), blk.vol_dtype, coords.data_ptr(), go.data_ptr(),
+                                            B, H, W, 4, r, gbuf.data_ptr(), None,
+                                            torch.cuda.current_stream().cuda_stream), "rc_lookup_bwd")
+    for l in range(4):
+        v = torch.as_strided(gbuf, (B * H * W, glay.H[l], glay.W[l]), (glay.slab[l], glay.pitch[l], 1), int(glay.offset[l]))
+        got = v.cpu().numpy() / 2.0
+        if l == 0:
+            rel_close(got.sum(axis=2), golden["dpyr0_rowsum"], 1e-4, "dpyr0 row sums")
+        else:
+            rel_close(got, golden[f"dpyr{l}"], 1e-4, f"dpyr{l}")
+
+
+def test_training_accumulates_over_iterations():
+    """Several lookups share one gradient pyramid; the build backward runs once."""
+    rng = np.random.default_rng(9)
+    B, D, H, W, r = 1, 16, 16, 24, 3
+    f1n = rng.standard_normal((B, D, H, W)).astype(np.float32)
+    f2n = rng.standard_normal((B, D, H, W)).astype(np.float32)
+    cs = [(O.coords_grid(B, H, W) + rng.normal(0, 2, (B, 2, H, W))).astype(np.float32) for _ in range(3)]
+    gs = [rng.standard_normal((B, 4 * 49, H, W)).astype(np.float32) for _ in range(3)]
+    f1 = t(f1n).requires_grad_(True)
+    f2 = t(f2n).requires_grad_(True)
+    blk = R.CorrBlock(f1, f2, 4, r, storage="fp32", math="fp32")
+    loss = sum((blk(t(c)) * t(g)).sum() for c, g in zip(cs, gs))
+    loss.backward()
+    pyr = O.corr_pyramid(f1n.astype(np.float64), f2n.astype(np.float64), 4)
+    acc = None
+    for c, g in zip(cs, gs):
+        dp, _ = O.window_lookup_backward(pyr, c, r, g)
+        acc = dp if acc is None else [a + b for a, b in zip(acc, dp)]
+    d1, d2 = O.pyramid_backward(acc, f1n, f2n)
+    rel_close(f1.grad.cpu().numpy(), d1, 1e-3, "dfmap1 over 3 iterations")
+    rel_close(f2.grad.cpu().numpy(), d2, 1e-3, "dfmap2 over 3 iterations")
+
+
+# ------------------------------------------------------------------ on-the-fly path
+@pytest.mark.parametrize("kind", KINDS)
+def test_alternate_block_matches_reference(golden, kind):
+    blk = R.AlternateCorrBlock(t(golden["fmap1"]), t(golden["fmap2"]), 4, int(golden["radius"]))
+    out = blk(t(golden[f"coords_{kind}"]))
+    ref = golden[f"out_{kind}"]
+    assert tuple(out.shape) == ref.shape and out.dtype == torch.float32
+    rel_close(out.cpu().numpy(), ref, 1e-4, f"alt {kind}")   # fp32 path: 1e-4
+
+
+def test_alt_cuda_corr_forward_backward_contract():
+    rng = np.random.default_rng(4)
+    B, H1, W1, H2, W2, Cc, r = 2, 9, 13, 5, 7, 24, 3
+    f1 = rng.standard_normal((B, H1, W1, Cc)).astype(np.float32)
+    f2 = rng.standard_normal((B, H2, W2, Cc)).astype(np.float32)
+    coords = rng.uniform(-3, 9, (B, 1, H1, W1, 2)).astype(np.float32)
+    (corr,) = R.alt_cuda_corr.forward(t(f1), t(f2), t(coords), r)
+    assert tuple(corr.shape) == (B, 1, 49, H1, W1)
+    rel_close(corr.cpu().numpy(), O.alt_forward(f1, f2, coords, r), 1e-4, "alt_cuda_corr.forward")
+    g = rng.standard_normal(tuple(corr.shape)).astype(np.float32)
+    g1, g2, gc = R.alt_cuda_corr.backward(t(f1), t(f2), t(coords), t(g), r)
+    o1, o2, oc = O.alt_backward(f1, f2, coords, g, r)
+    rel_close(g1.cpu().numpy(), o1, 1e-4, "fmap1_grad")
+    rel_close(g2.cpu().numpy(), o2, 1e-4, "fmap2_grad")
+    assert tuple(gc.shape) == coords.shape and not gc.any().item()   # zeros, as in the reference
+
+
+def test_alternate_equals_default_at_sintel_shape():
+    rng = np.random.default_rng(2)
+    B, D, H, W = 1, 256, 55, 128
+    f1 = t(rng.standard_normal((B, D, H, W)).astype(np.float32))
+    f2 = t(rng.standard_normal((B, D, H, W)).astype(np.float32))
+    c = R.coords_grid(B, H, W, dev()) + 5 * torch.randn(B, 2, H, W, device=dev())
+    a = R.AlternateCorrBlock(f1, f2, 4, 4)(c)
+    d = R.CorrBlock(f1, f2, 4, 4, storage="fp32", math="fp32")(c)
+    rel_close(a.cpu().numpy(), d.cpu().numpy(), 1e-4, "alt vs default, fp32")
+    h = R.CorrBlock(f1, f2, 4, 4)(c)
+    rel_close(h.cpu().numpy(), d.cpu().numpy(), 1e-2, "bf16 tensor-core vs fp32, full size")
+
+
+# ------------------------------------------------------------------ full-size properties
+def test_full_size_properties_sintel_batch():
+    """Size-independent checks at the BASELINE shape (55x128x256, batch 2)."""
+    B, D, H, W, r = 2, 256, 55, 128, 4
+    g = torch.Generator(device="cpu").manual_seed(0)
+    f1 = torch.randn(B, D, H, W, generator=g).to(dev())
+    f2 = torch.randn(B, D, H, W, generator=g).to(dev())
+    blk = R.CorrBlock(f1, f2, 4, r)
+    grid = R.coords_grid(B, H, W, dev())
+    # integer coordinates: the centre tap of level 0 is the volume entry itself
+    out = blk(grid)
+    pyr0 = blk.corr_pyramid[0]
+    n = 2 * r + 1
+    centre = out[:, r * n + r]                                   # [B,H,W]
+    q = torch.arange(B * H * W, device=dev())
+    yy = (q % (H * W)) // W
+    xx = q % W
+    direct = pyr0[q, 0, yy, xx].float().view(B, H, W)
+    assert torch.equal(centre, direct)
+    # linearity in fmap1: doubling features doubles every sample (powers of two are exact in bf16)
+    out2 = R.CorrBlock(2 * f1, f2, 4, r)(grid + 0.25)
+    out1 = blk(grid + 0.25)
+    assert torch.allclose(out2, 2 * out1, rtol=0, atol=0)
+    # pooling: each level-1 cell is the mean of its four level-0 cells (up to bf16 rounding)
+    p0 = blk.corr_pyramid[0][:, 0].float()
+    p1 = blk.corr_pyramid[1][:, 0].float()
+    m = 0.25 * (p0[:, 0:2 * (H // 2):2, 0:2 * (W // 2):2] + p0[:, 1:2 * (H // 2):2, 0:2 * (W // 2):2]
+                + p0[:, 0:2 * (H // 2):2, 1:2 * (W // 2):2] + p0[:, 1:2 * (H // 2):2, 1:2 * (W // 2):2])
+    assert (p1 - m).abs().max().item() < 0.02
+    # batch independence: pair 1 alone gives the same bits
+    solo = R.CorrBlock(f1[1:], f2[1:], 4, r)(grid[1:] + 0.25)
+    assert torch.equal(solo, out1[1:])
+
+
+# ------------------------------------------------------------------ interface / errors
+def test_rejects_cpu_tensors_and_bad_shapes():
+    with pytest.raises(RuntimeError):
+        R.CorrBlock(torch.zeros(1, 8, 16, 16), torch.zeros(1, 8, 16, 16))
+    f = torch.zeros(1, 8, 16, 16, device=dev())
+    with pytest.raises(RuntimeError):
+        R.CorrBlock(f, torch.zeros(1, 8, 16, 17, device=dev()))
+    blk = R.CorrBlock(f, f)
+    with pytest.raises(RuntimeError):
+        blk(torch.zeros(1, 2, 16, 17, device=dev()))
+    with pytest.raises(RuntimeError):
+        R.CorrBlock(f, f, radius=7)(torch.zeros(1, 2, 16, 16, device=dev()))
+    with pytest.raises(RuntimeError):
+        R.alt_cuda_corr.forward(torch.zeros(1, 4, 4, 8), torch.zeros(1, 4, 4, 8), torch.zeros(1, 1, 4, 4, 2), 4)
+    with pytest.raises(RuntimeError):   # non-contiguous, like CHECK_CONTIGUOUS
+        R.alt_cuda_corr.forward(torch.zeros(1, 4, 8, 4, device=dev()).transpose(2, 3), torch.zeros(1, 4, 4, 8, device=dev()),
+                                torch.zeros(1, 1, 4, 4, 2, device=dev()), 4)
+
+
+def test_non_default_stream_and_noncontiguous_inputs():
+    rng = np.random.default_rng(8)
+    f1 = t(rng.standard_normal((1, 16, 32, 16)).astype(np.float32)).transpose(2, 3)   # non-contiguous [1,16,16,32]
+    f2 = t(rng.standard_normal((1, 16, 16, 32)).astype(np.float32))
+    c = R.coords_grid(1, 16, 32, dev()) + 0.5
+    ref = R.CorrBlock(f1, f2, storage="fp32", math="fp32")(c)
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        got = R.CorrBlock(f1, f2, storage="fp32", math="fp32")(c)
+    s.synchronize()
+    assert torch.equal(ref, got)
