@@ -93,6 +93,36 @@ RC_API int rc_build_pyramid(const float *fmap1, const float *fmap2, int B, int D
                      void *workspace, size_t workspace_bytes, rc_stream_t stream);
 
 /*
+ * rc_build_pyramid for callers that cannot allocate device memory.
+ * (No counterpart in the reference: its torch ops allocate freely.)
+ *
+ * Some hosts of this library may not call cudaMalloc at the point where they
+ * need a volume: a real-time tracker that fixed its memory plan at start-up, a
+ * plugin running inside another framework's arena, code between allocator
+ * checkpoints.  They still own the inputs and the output pyramid, but have
+ * nowhere to put the repacked bf16 features the tensor-core build needs.  This
+ * entry point keeps that scratch in a fixed array inside the library
+ * (RC_STATIC_SCRATCH_BYTES, resident on every GPU that loads the library until
+ * the process exits) and allocates nothing: no cudaMalloc / cudaFree, no
+ * allocating library routine.
+ *
+ * Same arguments and result as rc_build_pyramid(..., RC_MATH_BF16, ...) minus the
+ * workspace.  Limits and caveats:
+ *   - rc_build_workspace_bytes(B, D, H, W, RC_MATH_BF16) must not exceed
+ *     RC_STATIC_SCRATCH_BYTES (one or two Sintel-size pairs); larger requests
+ *     fail with RC_ESIZE and launch nothing.
+ *   - The first call on each device looks the array's device address up
+ *     (cudaGetSymbolAddress); make that first call outside any stream capture.
+ *   - All calls on a device share the one array.  Nothing in it has to start
+ *     at zero (every call rewrites the part it uses), but two calls whose
+ *     kernels overlap on the GPU -- different streams, no ordering between them
+ *     -- race on it.  Keep them on one stream or order them with events.
+ */
+#define RC_STATIC_SCRATCH_BYTES (16u << 20)
+RC_API int rc_build_pyramid_static(const float *fmap1, const float *fmap2, int B, int D, int H, int W,
+                                   int num_levels, int vol_dtype, void *pyramid, rc_stream_t stream);
+
+/*
  * Windowed bilinear lookup over all levels in one launch.  Replaces
  * CorrBlock.__call__ (core/corr.py:29-50) together with bilinear_sampler /
  * F.grid_sample(align_corners=True, zeros padding) (core/utils/utils.py:57-65).

@@ -9,6 +9,7 @@ RC_MAX_LEVELS = 6
 RC_VOL_F32, RC_VOL_BF16 = 0, 1
 RC_MATH_F32, RC_MATH_BF16, RC_MATH_TF32 = 0, 1, 2
 RC_ABI_VERSION = 1
+RC_STATIC_SCRATCH_BYTES = 16 << 20
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libraftcorr.so")
@@ -33,6 +34,7 @@ SIGNATURES = {
     "rc_pyramid_layout": (_i, [_i, _i, _i, _i, _i, C.POINTER(Layout)]),
     "rc_build_workspace_bytes": (_i64, [_i, _i, _i, _i, _i]),
     "rc_build_pyramid": (_i, [_p, _p, _i, _i, _i, _i, _i, _i, _i, _p, _p, _sz, _p]),
+    "rc_build_pyramid_static": (_i, [_p, _p, _i, _i, _i, _i, _i, _i, _p, _p]),
     "rc_lookup_fwd": (_i, [_p, _i, _p, _i, _i, _i, _i, _i, _p, _p]),
     "rc_lookup_bwd": (_i, [_p, _i, _p, _p, _i, _i, _i, _i, _i, _p, _p, _p]),
     "rc_build_bwd_workspace_bytes": (_i64, [_i, _i, _i, _i, _i]),

@@ -35,6 +35,27 @@ int launch_build_bwd(const float *grad_pyramid, const float *fmap1, const float 
                      int H, int W, const rc_layout &glay, float *dfmap1, float *dfmap2, void *workspace,
                      size_t workspace_bytes, cudaStream_t s);
 
+// Scratch of rc_build_pyramid_static: the packed bf16 operands of the tensor-core
+// build.  In host code this name is only a handle for cudaGetSymbolAddress; the
+// kernels get the looked-up device pointer.
+static __device__ __align__(256) unsigned char g_static_scratch[RC_STATIC_SCRATCH_BYTES];
+
+// Device address of g_static_scratch on the current device, looked up once per device.
+static int static_scratch_ptr(void **out) {
+  static void *cache[64] = {};
+  int dev = 0;
+  RC_CUDA(cudaGetDevice(&dev));
+  RC_REQUIRE(dev >= 0 && dev < 64, "device index %d out of range", dev);
+  void *p = __atomic_load_n(&cache[dev], __ATOMIC_ACQUIRE);
+  if (p == nullptr) {
+    RC_CUDA(cudaGetSymbolAddress(&p, g_static_scratch));
+    RC_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned a null address");
+    __atomic_store_n(&cache[dev], p, __ATOMIC_RELEASE);   // same value from any thread
+  }
+  *out = p;
+  return RC_OK;
+}
+
 static int make_layout(int B, int H, int W, int num_levels, int vol_dtype, rc_layout *out) {
   RC_REQUIRE(out != nullptr, "rc_pyramid_layout: out is NULL");
   RC_REQUIRE(B >= 1 && H >= 1 && W >= 1, "rc_pyramid_layout: bad sizes B=%d H=%d W=%d", B, H, W);
@@ -117,6 +138,32 @@ int rc_build_pyramid(const float *fmap1, const float *fmap2, int B, int D, int H
   r = launch_pack(fmap1, fmap2, B, D, H, W, math, f1p, f2p, s);
   if (r) return r;
   return launch_build_tc(f1p, f2p, B, D, H, W, lay, vol_dtype, math, pyramid, s);
+}
+
+int rc_build_pyramid_static(const float *fmap1, const float *fmap2, int B, int D, int H, int W,
+                            int num_levels, int vol_dtype, void *pyramid, rc_stream_t stream) {
+  RC_REQUIRE(fmap1 && fmap2 && pyramid, "rc_build_pyramid_static: NULL pointer");
+  RC_REQUIRE(D >= 1, "rc_build_pyramid_static: D=%d", D);
+  rc_layout lay;
+  int r = make_layout(B, H, W, num_levels, vol_dtype, &lay);
+  if (r) return r;
+  const int64_t need = rc_build_workspace_bytes(B, D, H, W, RC_MATH_BF16);
+  if (need < 0 || need > (int64_t)RC_STATIC_SCRATCH_BYTES) {
+    set_error("rc_build_pyramid_static: B=%d D=%d H=%d W=%d needs %lld bytes of scratch, the built-in "
+              "array holds %u; use rc_build_pyramid with a caller-owned workspace",
+              B, D, H, W, (long long)need, (unsigned)RC_STATIC_SCRATCH_BYTES);
+    return RC_ESIZE;
+  }
+  RC_REQUIRE(((uintptr_t)pyramid & 255) == 0, "pyramid must be 256-byte aligned");
+  void *scratch = nullptr;
+  r = static_scratch_ptr(&scratch);
+  if (r) return r;
+  cudaStream_t s = (cudaStream_t)stream;
+  void *f1p = scratch;
+  void *f2p = (char *)scratch + round_up64((int64_t)B * H * W * D * 2, 1024);
+  r = launch_pack(fmap1, fmap2, B, D, H, W, RC_MATH_BF16, f1p, f2p, s);
+  if (r) return r;
+  return launch_build_tc(f1p, f2p, B, D, H, W, lay, vol_dtype, RC_MATH_BF16, pyramid, s);
 }
 
 int rc_lookup_fwd(const void *pyramid, int vol_dtype, const float *coords, int B, int H, int W,
