@@ -28,7 +28,7 @@ extern "C" {
 #define RC_API
 #endif
 
-#define RC_ABI_VERSION 1
+#define RC_ABI_VERSION 2
 #define RC_MAX_LEVELS 6
 
 /* error codes */
@@ -50,19 +50,30 @@ typedef struct CUstream_st *rc_stream_t;   /* == cudaStream_t */
 
 /*
  * Memory layout of the pooled correlation pyramid (all levels in ONE buffer).
- * Level l holds, for every query (b, q), a slab of H[l] rows with a padded
- * row pitch:  element (b, q, y, x) of level l lives at
- *     offset[l] + ((size_t)b * N + q) * slab[l] + y * pitch[l] + x.
- * H[l] = H >> l and W[l] = W >> l, which is what three floor-truncating
- * avg_pool2d(2, 2) calls give (core/corr.py:24-27).  Units are elements.
+ *
+ * Level l holds, for every query (b, q), a slab: the H[l] x W[l] map of that
+ * query's correlations (H[l] = H >> l, W[l] = W >> l: what three
+ * floor-truncating avg_pool2d(2, 2) calls give, core/corr.py:24-27), cut into
+ * TILES of tile_h = 4 rows x tile_w columns, tile_w = 16 bytes of elements
+ * (8 bf16 / 4 fp32), so that one tile is 64 contiguous, 64-byte-aligned bytes:
+ * the unit in which B200's L2 fetches from HBM.  A (2r+2)^2 lookup window then
+ * touches ~7 tiles instead of 10 half-used row pieces.  Tiles are stored row
+ * by row; element (b, q, y, x) of level l lives at (units: elements)
+ *     offset[l] + ((size_t)b * N + q) * slab[l]
+ *               + ((y / 4) * tiles_x[l] + x / tile_w) * (4 * tile_w)
+ *               + (y % 4) * tile_w + x % tile_w.
+ * Elements of edge tiles beyond H[l] / W[l] are PADDING; every producer in this
+ * library writes zeros there and the lookup relies on it.
  */
 typedef struct rc_layout {
   int32_t num_levels;
   int32_t B, N;                    /* N = H * W queries per pair */
+  int32_t tile_h, tile_w;          /* 4, and 8 (bf16) or 4 (fp32) */
   int32_t H[RC_MAX_LEVELS];
   int32_t W[RC_MAX_LEVELS];
-  int32_t pitch[RC_MAX_LEVELS];
-  int64_t slab[RC_MAX_LEVELS];
+  int32_t tiles_y[RC_MAX_LEVELS];  /* ceil(H[l] / tile_h) */
+  int32_t tiles_x[RC_MAX_LEVELS];  /* ceil(W[l] / tile_w) */
+  int64_t slab[RC_MAX_LEVELS];     /* tiles_y * tiles_x * tile_h * tile_w */
   int64_t offset[RC_MAX_LEVELS];
   int64_t total_elems;             /* size of the whole buffer, elements */
   int32_t elem_bytes;              /* 4 (RC_VOL_F32) or 2 (RC_VOL_BF16) */

@@ -8,7 +8,7 @@ import os
 RC_MAX_LEVELS = 6
 RC_VOL_F32, RC_VOL_BF16 = 0, 1
 RC_MATH_F32, RC_MATH_BF16, RC_MATH_TF32 = 0, 1, 2
-RC_ABI_VERSION = 1
+RC_ABI_VERSION = 2
 RC_STATIC_SCRATCH_BYTES = 16 << 20
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
@@ -19,8 +19,9 @@ class Layout(C.Structure):
     """mirror of struct rc_layout"""
     _fields_ = [
         ("num_levels", C.c_int32), ("B", C.c_int32), ("N", C.c_int32),
+        ("tile_h", C.c_int32), ("tile_w", C.c_int32),
         ("H", C.c_int32 * RC_MAX_LEVELS), ("W", C.c_int32 * RC_MAX_LEVELS),
-        ("pitch", C.c_int32 * RC_MAX_LEVELS),
+        ("tiles_y", C.c_int32 * RC_MAX_LEVELS), ("tiles_x", C.c_int32 * RC_MAX_LEVELS),
         ("slab", C.c_int64 * RC_MAX_LEVELS), ("offset", C.c_int64 * RC_MAX_LEVELS),
         ("total_elems", C.c_int64), ("elem_bytes", C.c_int32),
     ]
@@ -84,3 +85,35 @@ def pyramid_layout(B: int, H: int, W: int, num_levels: int, vol_dtype: int) -> L
     lay = Layout()
     check(lib().rc_pyramid_layout(B, H, W, num_levels, vol_dtype, C.byref(lay)), "rc_pyramid_layout")
     return lay
+
+
+def _tiled(buf, lay: Layout, level: int):
+    """5-D strided VIEW [B*N, tiles_y, tile_h, tiles_x, tile_w] of one level."""
+    import torch
+    th, tw = int(lay.tile_h), int(lay.tile_w)
+    ty, tx = int(lay.tiles_y[level]), int(lay.tiles_x[level])
+    q = int(lay.B) * int(lay.N)
+    return torch.as_strided(buf, (q, ty, th, tx, tw), (int(lay.slab[level]), tx * th * tw, tw, th * tw, 1),
+                            int(lay.offset[level]))
+
+
+def level_store(buf, lay: Layout, level: int, values) -> None:
+    """Inverse of level_view: write logical [B*N, H_l, W_l] values into the tiled
+    buffer, zeros into the padding (the invariant the lookup relies on)."""
+    import torch
+    v = _tiled(buf, lay, level)
+    q, ty, th, tx, tw = v.shape
+    full = torch.zeros(q, ty * th, tx * tw, dtype=buf.dtype, device=buf.device)
+    full[:, : int(lay.H[level]), : int(lay.W[level])] = values.to(device=buf.device, dtype=buf.dtype)
+    v.copy_(full.view(q, ty, th, tx, tw))
+
+
+def level_view(buf, lay: Layout, level: int):
+    """Logical [B*N, H_l, W_l] copy of one pyramid level out of the tiled buffer
+    (`buf`: flat torch tensor holding the whole pyramid).  The buffer keeps every
+    query's map in 64-byte tiles (see rc_layout in include/raft_corr.h), which no
+    strided view can express, so this gathers; it is meant for tests, debugging
+    and the `corr_pyramid` attribute, not for the hot path."""
+    v = _tiled(buf, lay, level)
+    q, ty, th, tx, tw = v.shape
+    return v.reshape(q, ty * th, tx * tw)[:, : int(lay.H[level]), : int(lay.W[level])]

@@ -141,14 +141,10 @@ class CorrBlock:
 
     @property
     def corr_pyramid(self) -> List[torch.Tensor]:
-        """Views [B*N, 1, H_l, W_l] over the pyramid buffer (row pitch padded)."""
-        lay = self.layout
-        views = []
-        for l in range(self.num_levels):
-            views.append(torch.as_strided(
-                self._buf, (self.B * lay.N, 1, lay.H[l], lay.W[l]),
-                (lay.slab[l], lay.slab[l], lay.pitch[l], 1), int(lay.offset[l])))
-        return views
+        """Levels as [B*N, 1, H_l, W_l] tensors, the reference's shape
+        (core/corr.py:21-27).  The buffer itself is tiled (rc_layout), so these
+        are gathered copies for inspection and tests; the lookup reads the buffer."""
+        return [_lib.level_view(self._buf, self.layout, l).unsqueeze(1) for l in range(self.num_levels)]
 
     @staticmethod
     def corr(fmap1, fmap2):

@@ -71,14 +71,16 @@ static int make_layout(int B, int H, int W, int num_levels, int vol_dtype, rc_la
   out->B = B;
   out->N = H * W;
   out->elem_bytes = vol_dtype == RC_VOL_BF16 ? 2 : 4;
-  // rows start on 32-byte sectors: 16 bf16 or 8 fp32 elements
-  const int align = 32 / out->elem_bytes;
+  // 64-byte tiles: 4 rows of 16 bytes
+  out->tile_h = TILE_H;
+  out->tile_w = 16 / out->elem_bytes;
   int64_t off = 0;
   for (int l = 0; l < num_levels; ++l) {
     out->H[l] = H >> l;
     out->W[l] = W >> l;
-    out->pitch[l] = (int)round_up64(out->W[l], align);
-    out->slab[l] = (int64_t)out->H[l] * out->pitch[l];
+    out->tiles_y[l] = ceil_div(out->H[l], out->tile_h);
+    out->tiles_x[l] = ceil_div(out->W[l], out->tile_w);
+    out->slab[l] = (int64_t)out->tiles_y[l] * out->tiles_x[l] * out->tile_h * out->tile_w;
     out->offset[l] = off;
     off += round_up64((int64_t)B * out->N * out->slab[l], 256);
   }

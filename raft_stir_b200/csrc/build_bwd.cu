@@ -7,8 +7,10 @@
 //   dfmap1[b,d,q]      = s * sum_l sum_t  dC_l[b,q,t] * pool_l(fmap2)[b,d,t]
 //   dpool_l[b,d,t]     = s * sum_q        dC_l[b,q,t] * fmap1[b,d,q]
 //   dfmap2[b,d,y,x]    = sum_l dpool_l[b,d,y>>l,x>>l] / 4^l      (inside level l's footprint)
-// with s = 1/sqrt(D).  The two contractions are plain fp32 GEMMs over the padded
-// slabs of the gradient pyramid (padding columns hold zeros) and go to cuBLAS
+// with s = 1/sqrt(D).  A slab of the gradient pyramid is the query's map in tile
+// order (rc_layout), i.e. a fixed permutation of the targets plus zero padding;
+// pool_l(fmap2) is laid out with the same permutation, so the two contractions
+// are plain fp32 GEMMs over whole slabs and go to cuBLAS
 // SGEMM, the same arithmetic the reference's autograd uses; the pooled/padded
 // copy of fmap2 and the fold back to fmap2's shape are small kernels here.
 #include <cublas_v2.h>
@@ -18,11 +20,10 @@
 namespace rc {
 namespace {
 
-// f2pad_l[b][d][y*pitch + x] = mean of the 2^l x 2^l block of fmap2[b][d], 0 in the padding
+// f2pad_l[b][d][tile_offset(y, x)] = mean of the 2^l x 2^l block of fmap2[b][d], 0 in the padding
 __global__ void __launch_bounds__(256)
 pool_pad_kernel(const float *__restrict__ fmap2, float *__restrict__ dst, int BD, int H, int W, int l,
-                int Hl, int Wl, int pitch) {
-  const long long per = (long long)Hl * pitch;
+                int Hl, int Wl, int tiles_x, long long per) {
   const long long total = (long long)BD * per;
   const int k = 1 << l;
   const float inv = 1.0f / (float)(k * k);
@@ -30,9 +31,11 @@ pool_pad_kernel(const float *__restrict__ fmap2, float *__restrict__ dst, int BD
        i += (long long)gridDim.x * blockDim.x) {
     const long long bd = i / per;
     const int r = (int)(i - bd * per);
-    const int y = r / pitch, x = r - y * pitch;
+    const int tile = r / Tile<float>::ELEMS, in = r - tile * Tile<float>::ELEMS;
+    const int y = (tile / tiles_x) * TILE_H + in / Tile<float>::W;
+    const int x = (tile % tiles_x) * Tile<float>::W + in % Tile<float>::W;
     float v = 0.f;
-    if (x < Wl) {
+    if (x < Wl && y < Hl) {
       const float *src = fmap2 + (size_t)bd * H * W + (size_t)(y * k) * W + x * k;
       for (int dy = 0; dy < k; ++dy)
         for (int dx = 0; dx < k; ++dx) v += src[(size_t)dy * W + dx];
@@ -44,7 +47,7 @@ pool_pad_kernel(const float *__restrict__ fmap2, float *__restrict__ dst, int BD
 
 struct FoldLevels {
   int L;
-  int Hl[RC_MAX_LEVELS], Wl[RC_MAX_LEVELS], pitch[RC_MAX_LEVELS];
+  int Hl[RC_MAX_LEVELS], Wl[RC_MAX_LEVELS], tiles_x[RC_MAX_LEVELS];
   long long off[RC_MAX_LEVELS];    // element offset of level l in the dpool buffer
   long long slab[RC_MAX_LEVELS];
 };
@@ -62,7 +65,7 @@ fold_kernel(const float *__restrict__ dpool, float *__restrict__ dfmap2, int BD,
     for (int l = 0; l < f.L; ++l, w *= 0.25f) {
       const int yl = y >> l, xl = x >> l;
       if (yl < f.Hl[l] && xl < f.Wl[l])
-        v += w * dpool[f.off[l] + bd * f.slab[l] + (size_t)yl * f.pitch[l] + xl];
+        v += w * dpool[f.off[l] + bd * f.slab[l] + tile_offset<float>(yl, xl, f.tiles_x[l])];
     }
     dfmap2[i] = v;
   }
@@ -101,7 +104,7 @@ int launch_build_bwd(const float *gpyr, const float *fmap1, const float *fmap2, 
   FoldLevels f{};
   f.L = L;
   for (int l = 0; l < L; ++l) {
-    f.Hl[l] = g.H[l]; f.Wl[l] = g.W[l]; f.pitch[l] = g.pitch[l];
+    f.Hl[l] = g.H[l]; f.Wl[l] = g.W[l]; f.tiles_x[l] = g.tiles_x[l];
     f.slab[l] = g.slab[l];
     f.off[l] = (long long)B * D * slabs;   // level l block: [B*D][slab_l]
     slabs += g.slab[l];
@@ -125,7 +128,8 @@ int launch_build_bwd(const float *gpyr, const float *fmap1, const float *fmap2, 
     float *f2l = f2pad + f.off[l];
     float *dpl = dpool + f.off[l];
     const long long total = (long long)B * D * g.slab[l];
-    pool_pad_kernel<<<grid_for(total), 256, 0, s>>>(fmap2, f2l, B * D, H, W, l, g.H[l], g.W[l], g.pitch[l]);
+    pool_pad_kernel<<<grid_for(total), 256, 0, s>>>(fmap2, f2l, B * D, H, W, l, g.H[l], g.W[l], g.tiles_x[l],
+                                                    g.slab[l]);
     RC_LAUNCH_CHECK("pool_pad_kernel");
     const float *dC = gpyr + g.offset[l];
     const int K = (int)g.slab[l];

@@ -6,7 +6,8 @@
 // and as the in-library cross-check of the tcgen05 build; the fast path is
 // build_tc.cu.  Level 0 is written by a 64x64-tile SGEMM that reads the NCHW
 // maps in place (both operands are pixel-contiguous, so no repack is needed);
-// levels 1.. are pooled by a second kernel.
+// levels 1.. are pooled by a second kernel.  The pyramid buffer is cleared
+// first so that the padding inside edge tiles is zero (rc_layout's invariant).
 #include "common.cuh"
 
 namespace rc {
@@ -29,7 +30,7 @@ __device__ __forceinline__ float from_vol(__nv_bfloat16 v) { return __bfloat162f
 template <typename VolT>
 __global__ void __launch_bounds__(256)
 build_level0_simt_kernel(const float *__restrict__ fmap1, const float *__restrict__ fmap2,
-                         VolT *__restrict__ lvl0, int D, int N, int W, int pitch, long long slab,
+                         VolT *__restrict__ lvl0, int D, int N, int W, int tiles_x, long long slab,
                          float scale) {
   __shared__ float As[SM_K][SM_T];
   __shared__ float Bs[SM_K][SM_T];
@@ -74,7 +75,7 @@ build_level0_simt_kernel(const float *__restrict__ fmap1, const float *__restric
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       int t = t0 + tx * 4 + j;
-      if (t < N) row[(size_t)(t / W) * pitch + (t % W)] = to_vol<VolT>(acc[i][j] * scale);
+      if (t < N) row[tile_offset<VolT>(t / W, t % W, tiles_x)] = to_vol<VolT>(acc[i][j] * scale);
     }
   }
 }
@@ -83,7 +84,7 @@ build_level0_simt_kernel(const float *__restrict__ fmap1, const float *__restric
 template <typename VolT>
 __global__ void __launch_bounds__(256)
 pool_level_kernel(const VolT *__restrict__ src, VolT *__restrict__ dst, long long slabs, int Hd,
-                  int Wd, int pitch_s, long long slab_s, int pitch_d, long long slab_d) {
+                  int Wd, int tiles_x_s, long long slab_s, int tiles_x_d, long long slab_d) {
   const long long per = (long long)Hd * Wd;
   const long long total = slabs * per;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
@@ -91,9 +92,12 @@ pool_level_kernel(const VolT *__restrict__ src, VolT *__restrict__ dst, long lon
     long long s = i / per;
     int r = (int)(i - s * per);
     int y = r / Wd, x = r - y * Wd;
-    const VolT *p = src + s * slab_s + (size_t)(2 * y) * pitch_s + 2 * x;
-    float v = 0.25f * (from_vol(p[0]) + from_vol(p[1]) + from_vol(p[pitch_s]) + from_vol(p[pitch_s + 1]));
-    dst[s * slab_d + (size_t)y * pitch_d + x] = to_vol<VolT>(v);
+    const VolT *p = src + s * slab_s;
+    float v = 0.25f * (from_vol(p[tile_offset<VolT>(2 * y, 2 * x, tiles_x_s)]) +
+                       from_vol(p[tile_offset<VolT>(2 * y, 2 * x + 1, tiles_x_s)]) +
+                       from_vol(p[tile_offset<VolT>(2 * y + 1, 2 * x, tiles_x_s)]) +
+                       from_vol(p[tile_offset<VolT>(2 * y + 1, 2 * x + 1, tiles_x_s)]));
+    dst[s * slab_d + tile_offset<VolT>(y, x, tiles_x_d)] = to_vol<VolT>(v);
   }
 }
 
@@ -101,9 +105,10 @@ template <typename VolT>
 int build_simt_t(const float *fmap1, const float *fmap2, int B, int D, int H, int W,
                  const rc_layout &lay, VolT *pyr, cudaStream_t s) {
   const int N = H * W;
+  RC_CUDA(cudaMemsetAsync(pyr, 0, (size_t)lay.total_elems * sizeof(VolT), s));
   dim3 grid(ceil_div(N, SM_T), ceil_div(N, SM_T), B);
   build_level0_simt_kernel<VolT><<<grid, 256, 0, s>>>(fmap1, fmap2, pyr + lay.offset[0], D, N, W,
-                                                      lay.pitch[0], lay.slab[0],
+                                                      lay.tiles_x[0], lay.slab[0],
                                                       1.0f / sqrtf((float)D));
   RC_LAUNCH_CHECK("build_level0_simt_kernel");
   return RC_OK;
@@ -117,8 +122,8 @@ int pool_levels_t(const rc_layout &lay, VolT *pyr, int first_level, cudaStream_t
     if (total == 0) continue;
     int blocks = (int)((total + 255) / 256 < 148LL * 32 ? (total + 255) / 256 : 148LL * 32);
     pool_level_kernel<VolT><<<blocks, 256, 0, s>>>(pyr + lay.offset[l - 1], pyr + lay.offset[l],
-                                                   slabs, lay.H[l], lay.W[l], lay.pitch[l - 1],
-                                                   lay.slab[l - 1], lay.pitch[l], lay.slab[l]);
+                                                   slabs, lay.H[l], lay.W[l], lay.tiles_x[l - 1],
+                                                   lay.slab[l - 1], lay.tiles_x[l], lay.slab[l]);
     RC_LAUNCH_CHECK("pool_level_kernel");
   }
   return RC_OK;

@@ -40,15 +40,44 @@ constexpr int TC_THREADS = 192;
 constexpr int EPI_WARP0 = 2;
 
 struct TcParams {
-  int N, MT, NT, nbx, KB, num_levels, stages;
-  int total_tiles;
+  int B, N, MT, NT, nbx, KB, num_levels, stages;
+  int group_pairs, num_groups;      // pairs processed together (see TileWalk)
   float scale;
-  // level 3 of a bf16 volume is 8-byte rows: below TMA's 16-byte minimum, stored directly
-  void *l3_ptr;
-  long long l3_slab;
-  int l3_pitch, l3_H, l3_W;
-  // level extents for skipping fully out-of-range stores
-  int Hl[4], Wl[4];
+  // pyramid geometry (levels >= num_levels are unused)
+  int Hl[4], Wl[4], tiles_y[4], tiles_x[4];
+  long long slab[4];                // elements per query
+  void *lvl[4];                     // base pointer of each level
+};
+
+// Order in which a CTA visits (pair, query block, target block) tiles.  Pairs are
+// taken in groups of `group_pairs`; inside a group every CTA gets one contiguous
+// range of the group's tiles (balanced to within one tile, and a range stays on
+// one query block for NT tiles so the A operand is reloaded rarely).  Grouping
+// keeps the packed fmap2 of only a few pairs hot in L2 next to the output stream;
+// one range over all pairs has every pair's operand in flight at once and misses.
+struct TileWalk {
+  int grp;
+  long long t, t_end, base;
+  __device__ __forceinline__ void init() { grp = -1; t = 0; t_end = 0; base = 0; }
+  // next global tile index ((b * MT + m) * NT + n), or false when done
+  __device__ __forceinline__ bool next(const TcParams &p, long long &gt) {
+    while (t >= t_end) {
+      ++grp;
+      if (grp >= p.num_groups) return false;
+      const int pair0 = grp * p.group_pairs;
+      const int np = min(p.group_pairs, p.B - pair0);
+      const long long tpp = (long long)p.MT * p.NT;
+      const long long tot = np * tpp;
+      t = tot * blockIdx.x / gridDim.x;
+      t_end = tot * (blockIdx.x + 1) / gridDim.x;
+      base = pair0 * tpp;
+    }
+    gt = base + t;
+    ++t;
+    return true;
+  }
+  // is `gt` the last tile of this CTA's current range?
+  __device__ __forceinline__ bool range_ends() const { return t >= t_end; }
 };
 
 // ---------------------------------------------------------------- PTX wrappers
@@ -144,64 +173,77 @@ constexpr uint32_t IDESC_BF16 = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)
                                 ((uint32_t)(BM >> 4) << 24);
 
 // ---------------------------------------------------------------- epilogue staging
+// An epilogue thread owns one query (TMEM lane) and sees the 8x32 target block
+// two rows at a time.  Level 0 is written in STEPS of 256 bytes per query (bf16:
+// 4 block rows = one row of 4 tiles, contiguous; fp32: 2 block rows = half of a
+// row of 8 tiles, 8 pieces of 32 bytes): the thread parks its 16-byte units in a
+// per-warp buffer, then the warp reads the buffer back query by query and issues
+// coalesced 16-byte stores (a full 256-byte chunk per half warp).  Levels 1..3
+// of the block (168 / 336 bytes per query) collect in a second buffer and leave
+// once per tile the same way.
 template <typename VolT>
 struct Stg;
 template <>
 struct Stg<__nv_bfloat16> {
   static constexpr int ES = 2;
-  static constexpr int OFF_L0 = 0, OFF_L1 = 4096, OFF_L2 = 5120, OFF_L3 = 5632, BYTES = 6144;
-  static constexpr bool L3_TMA = false;
+  static constexpr int TW = 8;            // tile width, elements
+  static constexpr int L0_TILES = 4;      // level-0 tiles per block row of tiles
+  static constexpr int ROWS_PER_STEP = 4;
+  static constexpr int L1_UNITS = 8, L2_UNITS = 2;      // 16-byte units per query
+  static constexpr int NU = 11;           // L1 (8) + L2 (2) + L3 (1) units per query
 };
 template <>
 struct Stg<float> {
   static constexpr int ES = 4;
-  static constexpr int OFF_L0 = 0, OFF_L1 = 8192, OFF_L2 = 10240, OFF_L3 = 11264, BYTES = 12288;
-  static constexpr bool L3_TMA = true;
+  static constexpr int TW = 4;
+  static constexpr int L0_TILES = 8;
+  static constexpr int ROWS_PER_STEP = 2;
+  static constexpr int L1_UNITS = 16, L2_UNITS = 4;
+  static constexpr int NU = 21;
 };
+constexpr int STEP_BYTES = 32 * 256;      // per-warp level-0 step buffer
+template <typename VolT>
+constexpr int stage_bytes_per_warp() { return STEP_BYTES + 32 * Stg<VolT>::NU * 16; }
 
-// Write NV fp32 values (one row segment of this thread's query) into the staging
-// row `lane` of a [32 rows x RB bytes] box laid out with the TMA swizzle of span RB.
-template <typename VolT, int NV>
-__device__ __forceinline__ void stage_row(uint32_t base, int lane, const float *v) {
-  constexpr int RB = NV * (int)sizeof(VolT);
-  constexpr int CH = RB / 16;
-  const uint32_t row = base + lane * RB;
-  const int sw = ((lane * RB) >> 7) & (CH - 1);
-#pragma unroll
-  for (int j = 0; j < CH; ++j) {
-    uint32_t w0, w1, w2, w3;
-    if (sizeof(VolT) == 4) {
-      w0 = __float_as_uint(v[4 * j + 0]); w1 = __float_as_uint(v[4 * j + 1]);
-      w2 = __float_as_uint(v[4 * j + 2]); w3 = __float_as_uint(v[4 * j + 3]);
-    } else {
-      __nv_bfloat162 p0 = __floats2bfloat162_rn(v[8 * j + 0], v[8 * j + 1]);
-      __nv_bfloat162 p1 = __floats2bfloat162_rn(v[8 * j + 2], v[8 * j + 3]);
-      __nv_bfloat162 p2 = __floats2bfloat162_rn(v[8 * j + 4], v[8 * j + 5]);
-      __nv_bfloat162 p3 = __floats2bfloat162_rn(v[8 * j + 6], v[8 * j + 7]);
-      w0 = *reinterpret_cast<uint32_t *>(&p0); w1 = *reinterpret_cast<uint32_t *>(&p1);
-      w2 = *reinterpret_cast<uint32_t *>(&p2); w3 = *reinterpret_cast<uint32_t *>(&p3);
-    }
-    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(row + ((j ^ sw) << 4)), "r"(w0), "r"(w1),
-                 "r"(w2), "r"(w3)
-                 : "memory");
-  }
+__device__ __forceinline__ void sts16(uint32_t addr, uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
+}
+__device__ __forceinline__ uint4 lds16(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+  __nv_bfloat162 p = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t *>(&p);
+}
+// 16-byte unit number `n` of a value row (8 bf16 or 4 fp32 elements) -> smem
+template <typename VolT>
+__device__ __forceinline__ void put_unit(uint32_t addr, const float *v) {
+  if (sizeof(VolT) == 2)
+    sts16(addr, pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+  else
+    sts16(addr, __float_as_uint(v[0]), __float_as_uint(v[1]), __float_as_uint(v[2]), __float_as_uint(v[3]));
+}
+// step buffer: query row of 256 bytes, unit index XOR-rotated by the query so that
+// both the query-major writes and the unit-major read-back are conflict-free
+__device__ __forceinline__ uint32_t step_addr(uint32_t buf, int q, int unit) {
+  return buf + q * 256 + ((unit ^ (q & 7)) << 4);
 }
 
 // ---------------------------------------------------------------- the kernel
 template <typename VolT>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-                        const __grid_constant__ CUtensorMap map_l0, const __grid_constant__ CUtensorMap map_l1,
-                        const __grid_constant__ CUtensorMap map_l2, const __grid_constant__ CUtensorMap map_l3,
                         const TcParams p) {
   using S = Stg<VolT>;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  // carve (all offsets multiples of 1024)
+  // carve (operand offsets are multiples of 1024)
   uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const uint32_t sA = smem_u32(smem);
   const uint32_t sB = sA + p.KB * A_KB_BYTES;
   const uint32_t sStage = sB + p.stages * B_ST_BYTES;
-  const uint32_t sBar = sStage + 4 * 2 * S::BYTES;
+  const uint32_t sBar = sStage + 4 * stage_bytes_per_warp<VolT>();
   uint32_t *tmem_slot = (uint32_t *)(smem + (sBar - sA) + 128);
   // barrier table (8 bytes each)
   const uint32_t bar_a_full = sBar, bar_a_empty = sBar + 8;
@@ -211,10 +253,6 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
   const uint32_t bar_t_empty = bar_t_full + 16;     // [2]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-
-  // contiguous tile range of this CTA
-  const long long t_begin = (long long)p.total_tiles * blockIdx.x / gridDim.x;
-  const long long t_end = (long long)p.total_tiles * (blockIdx.x + 1) / gridDim.x;
 
   if (warp == 0 && lane == 0) {
     mbar_init(bar_a_full, 1);
@@ -241,11 +279,13 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
   if (warp == 0) {
     // ===================================================== TMA producer
     if (lane == 0) {
-      long long cur_key = -1;
+      TileWalk walk;
+      walk.init();
+      long long cur_key = -1, gt;
       uint32_t a_loads = 0, bs = 0;
-      for (long long t = t_begin; t < t_end; ++t) {
-        const long long key = t / p.NT;          // (b, m)
-        const int n = (int)(t - key * p.NT);
+      while (walk.next(p, gt)) {
+        const long long key = gt / p.NT;          // (b, m)
+        const int n = (int)(gt - key * p.NT);
         const int b = (int)(key / p.MT), m = (int)(key - (long long)b * p.MT);
         if (key != cur_key) {
           if (a_loads > 0) mbar_wait(bar_a_empty, (a_loads - 1) & 1);
@@ -266,10 +306,13 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
   } else if (warp == 1) {
     // ===================================================== MMA issuer
     if (lane == 0) {
-      long long cur_key = -1;
+      TileWalk walk;
+      walk.init();
+      long long cur_key = -1, gt;
+      bool have = walk.next(p, gt);
       uint32_t a_uses = 0, bs = 0, i = 0;
-      for (long long t = t_begin; t < t_end; ++t, ++i) {
-        const long long key = t / p.NT;
+      while (have) {
+        const long long key = gt / p.NT;
         if (key != cur_key) {
           mbar_wait(bar_a_full, a_uses & 1);
           ++a_uses;
@@ -292,31 +335,46 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
           umma_commit(bar_b_empty + 8 * st);   // frees the B stage when these MMAs retire
         }
         umma_commit(bar_t_full + 8 * acc);     // accumulator ready
-        const bool last_of_key = (t + 1 >= t_end) || ((t + 1) / p.NT != key);
-        if (last_of_key) umma_commit(bar_a_empty);
+        long long gnext;
+        have = walk.next(p, gnext);
+        if (!have || gnext / p.NT != key) umma_commit(bar_a_empty);   // last use of this A operand
+        gt = gnext;
+        ++i;
       }
     }
   } else {
     // ===================================================== epilogue (4 warps)
     const int quarter = warp & 3;                 // TMEM lanes [32*quarter, +32)
-    const uint32_t stg0 = sStage + (warp - EPI_WARP0) * 2 * S::BYTES;
+    const uint32_t sbuf = sStage + (warp - EPI_WARP0) * stage_bytes_per_warp<VolT>();   // level-0 step buffer
+    const uint32_t pbuf = sbuf + STEP_BYTES;                                            // levels 1..3
     const int L = p.num_levels;
-    uint32_t i = 0, rpc = 0;
-    for (long long t = t_begin; t < t_end; ++t, ++i) {
-      const long long key = t / p.NT;
-      const int n = (int)(t - key * p.NT);
+    TileWalk walk;
+    walk.init();
+    long long gt;
+    uint32_t i = 0;
+    while (walk.next(p, gt)) {
+      const long long key = gt / p.NT;
+      const int n = (int)(gt - key * p.NT);
       const int b = (int)(key / p.MT), m = (int)(key - (long long)b * p.MT);
-      const int ty = n / p.nbx, tx = n - ty * p.nbx;
-      const int x0 = tx * TB_W, y0 = ty * TB_H;
-      const int qw = m * BM + quarter * 32;       // first query of this warp
+      const int by = n / p.nbx, bx = n - by * p.nbx;   // block coordinates (8 rows x 32 columns)
+      const int x0 = bx * TB_W, y0 = by * TB_H;
+      const int qw = m * BM + quarter * 32;            // first query of this warp
       const uint32_t acc = i & 1, use = i >> 1;
+      ++i;
       mbar_wait(bar_t_full + 8 * acc, use & 1);
       tc_fence_after();
       const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(quarter * 32) << 16);
+      const long long slab_q0 = (long long)b * p.N + qw;   // slab index of this warp's first query
+      const int nq = min(32, p.N - qw);                     // valid queries of this warp (may be <= 0)
+
+      // valid pooled cells of this block (floor rule of avg_pool2d; the rest is padding -> 0)
+      const int nvx1 = p.Wl[1] - (x0 >> 1), nvy1 = p.Hl[1] - (y0 >> 1);
+      const int nvx2 = p.Wl[2] - (x0 >> 2), nvy2 = p.Hl[2] - (y0 >> 2);
+      const int nvx3 = p.Wl[3] - (x0 >> 3), nvy3 = p.Hl[3] - (y0 >> 3);
 
       float p1prev[16], p2prev[8];
 #pragma unroll
-      for (int rp = 0; rp < 4; ++rp, ++rpc) {
+      for (int rp = 0; rp < 4; ++rp) {
         uint32_t r0[32], r1[32];
         tmem_ld32(taddr + (2 * rp) * 32, r0);
         tmem_ld32(taddr + (2 * rp + 1) * 32, r1);
@@ -327,44 +385,61 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
           __syncwarp();
           if (lane == 0) mbar_arrive(bar_t_empty + 8 * acc);
         }
-        const uint32_t buf = stg0 + (rpc & 1) * S::BYTES;
-        if (lane == 0) tma_store_wait_read<1>();   // the buffer used two row-pairs ago is drained
-        __syncwarp();
-
         float v0[32], v1[32], p1[16];
 #pragma unroll
         for (int k = 0; k < 32; ++k) {
           v0[k] = __uint_as_float(r0[k]) * p.scale;
           v1[k] = __uint_as_float(r1[k]) * p.scale;
         }
-        stage_row<VolT, 32>(buf + S::OFF_L0, lane, v0);
-        stage_row<VolT, 32>(buf + S::OFF_L0 + 32 * 32 * S::ES, lane, v1);
+        // ---- level 0 units of block rows 2rp, 2rp+1
+        if (sizeof(VolT) == 2) {
+          const int r = (2 * rp) & 3;                    // row inside the tile
 #pragma unroll
-        for (int k = 0; k < 16; ++k) p1[k] = 0.25f * ((v0[2 * k] + v0[2 * k + 1]) + (v1[2 * k] + v1[2 * k + 1]));
-        if (L > 1) stage_row<VolT, 16>(buf + S::OFF_L1, lane, p1);
-        float p2[8], p3[4];
+          for (int k = 0; k < 4; ++k) {
+            put_unit<VolT>(step_addr(sbuf, lane, k * 4 + r), v0 + 8 * k);
+            put_unit<VolT>(step_addr(sbuf, lane, k * 4 + r + 1), v1 + 8 * k);
+          }
+        } else {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            put_unit<VolT>(step_addr(sbuf, lane, k * 2), v0 + 4 * k);
+            put_unit<VolT>(step_addr(sbuf, lane, k * 2 + 1), v1 + 4 * k);
+          }
+        }
+        // ---- pooled levels, from the fp32 values
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+          const float a = 0.25f * ((v0[2 * k] + v0[2 * k + 1]) + (v1[2 * k] + v1[2 * k + 1]));
+          p1[k] = (k < nvx1 && rp < nvy1) ? a : 0.f;
+        }
+        if (L > 1) {
+#pragma unroll
+          for (int k = 0; k < 16 / S::TW; ++k) put_unit<VolT>(pbuf + (lane * S::NU + k * 4 + rp) * 16, p1 + S::TW * k);
+        }
         if (rp & 1) {
+          float p2[8];
 #pragma unroll
-          for (int k = 0; k < 8; ++k)
-            p2[k] = 0.25f * ((p1prev[2 * k] + p1prev[2 * k + 1]) + (p1[2 * k] + p1[2 * k + 1]));
-          if (L > 2) stage_row<VolT, 8>(buf + S::OFF_L2, lane, p2);
-          if (rp == 3) {
-#pragma unroll
-            for (int k = 0; k < 4; ++k)
-              p3[k] = 0.25f * ((p2prev[2 * k] + p2prev[2 * k + 1]) + (p2[2 * k] + p2[2 * k + 1]));
-            if (L > 3) {
-              if (S::L3_TMA) {
-                stage_row<VolT, 4>(buf + S::OFF_L3, lane, p3);
-              } else {
-                const int q = qw + lane, y3 = y0 >> 3, x3 = x0 >> 3;
-                if (q < p.N && y3 < p.l3_H) {
-                  VolT *dst = (VolT *)p.l3_ptr + ((size_t)b * p.N + q) * p.l3_slab + (size_t)y3 * p.l3_pitch + x3;
-#pragma unroll
-                  for (int k = 0; k < 4; ++k)
-                    if (x3 + k < p.l3_W) dst[k] = __float2bfloat16_rn(p3[k]);
-                }
-              }
+          for (int k = 0; k < 8; ++k) {
+            const float a = 0.25f * ((p1prev[2 * k] + p1prev[2 * k + 1]) + (p1[2 * k] + p1[2 * k + 1]));
+            p2[k] = (k < nvx2 && (rp >> 1) < nvy2) ? a : 0.f;
+          }
+          if (L > 2) {
+            if (sizeof(VolT) == 2) {
+              put_unit<VolT>(pbuf + (lane * S::NU + S::L1_UNITS + (rp >> 1)) * 16, p2);
+            } else {
+              put_unit<VolT>(pbuf + (lane * S::NU + S::L1_UNITS + (rp >> 1)) * 16, p2);
+              put_unit<VolT>(pbuf + (lane * S::NU + S::L1_UNITS + 2 + (rp >> 1)) * 16, p2 + 4);
             }
+          }
+          if (rp == 3) {
+            float p3[8];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              const float a = 0.25f * ((p2prev[2 * k] + p2prev[2 * k + 1]) + (p2[2 * k] + p2[2 * k + 1]));
+              p3[k] = (k < nvx3 && 0 < nvy3) ? a : 0.f;
+              p3[4 + k] = 0.f;
+            }
+            if (L > 3) put_unit<VolT>(pbuf + (lane * S::NU + S::L1_UNITS + S::L2_UNITS) * 16, p3);
           } else {
 #pragma unroll
             for (int k = 0; k < 8; ++k) p2prev[k] = p2[k];
@@ -373,25 +448,92 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
 #pragma unroll
           for (int k = 0; k < 16; ++k) p1prev[k] = p1[k];
         }
-        fence_async_smem();
-        __syncwarp();
-        if (lane == 0 && qw < p.N) {
-          const int ya = y0 + 2 * rp;
-          if (x0 < p.Wl[0]) {
-            if (ya < p.Hl[0]) tma_store_4d(&map_l0, buf + S::OFF_L0, x0, ya, qw, b);
-            if (ya + 1 < p.Hl[0]) tma_store_4d(&map_l0, buf + S::OFF_L0 + 32 * 32 * S::ES, x0, ya + 1, qw, b);
+
+        // ---- a level-0 step is complete: read it back query by query, coalesced stores
+        if (sizeof(VolT) == 4 || (rp & 1)) {
+          __syncwarp();
+          const int step = sizeof(VolT) == 2 ? (rp >> 1) : rp;
+          // tile row this step lands in, and the byte offset inside the tiles
+          const int ty = (y0 >> 2) + (sizeof(VolT) == 2 ? step : (step >> 1));
+          const int tx0 = x0 / S::TW;
+          const int nt = min(S::L0_TILES, p.tiles_x[0] - tx0);      // tiles of the chunk that exist
+          if (ty < p.tiles_y[0] && nt > 0) {
+            VolT *base = (VolT *)p.lvl[0] + ((long long)ty * p.tiles_x[0] + tx0) * (TILE_H * S::TW);
+            const int u = lane & 15;
+            // unit u of a query's step -> byte offset inside the chunk, and its tile
+            const int tile = sizeof(VolT) == 2 ? (u >> 2) : (u >> 1);
+            const int off = sizeof(VolT) == 2 ? u * 16 : (u >> 1) * 64 + (step & 1) * 32 + (u & 1) * 16;
+#pragma unroll 4
+            for (int it = 0; it < 16; ++it) {
+              const int ql = 2 * it + (lane >> 4);
+              const uint4 val = lds16(step_addr(sbuf, ql, u));
+              if (ql < nq && tile < nt)
+                *reinterpret_cast<uint4 *>((char *)(base + (slab_q0 + ql) * p.slab[0]) + off) = val;
+            }
           }
-          if (L > 1 && (x0 >> 1) < p.Wl[1] && (ya >> 1) < p.Hl[1])
-            tma_store_4d(&map_l1, buf + S::OFF_L1, x0 >> 1, ya >> 1, qw, b);
-          if ((rp & 1) && L > 2 && (x0 >> 2) < p.Wl[2] && (ya >> 2) < p.Hl[2])
-            tma_store_4d(&map_l2, buf + S::OFF_L2, x0 >> 2, ya >> 2, qw, b);
-          if (rp == 3 && L > 3 && S::L3_TMA && (x0 >> 3) < p.Wl[3] && (ya >> 3) < p.Hl[3])
-            tma_store_4d(&map_l3, buf + S::OFF_L3, x0 >> 3, ya >> 3, qw, b);
+          __syncwarp();
         }
-        if (lane == 0) tma_store_commit();
       }
+
+      // ---- levels 1..3 of this block
+      __syncwarp();
+      if (L > 1) {
+        constexpr int U1 = S::L1_UNITS, QPI = 32 / U1;       // units and queries per instruction
+        const int ty = y0 >> 3, tx0 = (x0 >> 1) / S::TW;
+        const int nt = min(U1 / 4, p.tiles_x[1] - tx0);
+        if (ty < p.tiles_y[1] && nt > 0) {
+          VolT *base = (VolT *)p.lvl[1] + ((long long)ty * p.tiles_x[1] + tx0) * (TILE_H * S::TW);
+          const int u = lane % U1;
+#pragma unroll 4
+          for (int it = 0; it < 32 / QPI; ++it) {
+            const int ql = it * QPI + lane / U1;
+            const uint4 val = lds16(pbuf + (ql * S::NU + u) * 16);
+            if (ql < nq && (u >> 2) < nt)
+              *reinterpret_cast<uint4 *>((char *)(base + (slab_q0 + ql) * p.slab[1]) + u * 16) = val;
+          }
+        }
+      }
+      if (L > 2) {
+        constexpr int U2 = S::L2_UNITS, QPI = 32 / U2;
+        const int ty = y0 >> 4, tx0 = (x0 >> 2) / S::TW;
+        const int row0 = (y0 >> 2) & 3;                       // first of the block's two rows inside the tile
+        if (ty < p.tiles_y[2]) {
+          VolT *base = (VolT *)p.lvl[2] + ((long long)ty * p.tiles_x[2] + tx0) * (TILE_H * S::TW);
+          const int u = lane % U2;
+          // bf16: units = rows 0,1 of one tile;  fp32: unit = tile * 2 + row ... stored as [row + 2*tile]
+          const int tile = sizeof(VolT) == 2 ? 0 : (u >> 1);
+          const int row = sizeof(VolT) == 2 ? u : (u & 1);
+          const int off = tile * 64 + (row0 + row) * 16;
+#pragma unroll
+          for (int it = 0; it < 32 / QPI; ++it) {
+            const int ql = it * QPI + lane / U2;
+            const uint4 val = lds16(pbuf + (ql * S::NU + S::L1_UNITS + (sizeof(VolT) == 2 ? u : row + 2 * tile)) * 16);
+            if (ql < nq && tx0 + tile < p.tiles_x[2])
+              *reinterpret_cast<uint4 *>((char *)(base + (slab_q0 + ql) * p.slab[2]) + off) = val;
+          }
+        }
+      }
+      if (L > 3) {
+        const int ty = y0 >> 5, tx = (x0 >> 3) / S::TW;
+        const int row = (y0 >> 3) & 3;
+        if (ty < p.tiles_y[3] && tx < p.tiles_x[3] && lane < nq) {
+          char *dst = (char *)((VolT *)p.lvl[3] + ((long long)ty * p.tiles_x[3] + tx) * (TILE_H * S::TW) +
+                               (slab_q0 + lane) * p.slab[3]) + row * 16;
+          const uint4 val = lds16(pbuf + (lane * S::NU + S::L1_UNITS + S::L2_UNITS) * 16);
+          if (sizeof(VolT) == 4) {
+            *reinterpret_cast<uint4 *>(dst) = val;
+          } else {
+            // 4 cells = 8 bytes: the left or right half of a tile row.  The left writer also
+            // zeroes the right half when no block to its right exists (padding columns).
+            const bool right = ((x0 >> 3) & 7) != 0;
+            if (right) *reinterpret_cast<uint2 *>(dst + 8) = make_uint2(val.x, val.y);
+            else if (bx + 1 < p.nbx) *reinterpret_cast<uint2 *>(dst) = make_uint2(val.x, val.y);
+            else *reinterpret_cast<uint4 *>(dst) = val;
+          }
+        }
+      }
+      __syncwarp();
     }
-    if (lane == 0) tma_store_wait_all();
   }
 
   tc_fence_before();
@@ -438,17 +580,9 @@ int encode(CUtensorMap *map, CUtensorMapDataType dt, int rank, const void *base,
   return RC_OK;
 }
 
-CUtensorMapSwizzle swizzle_for(int row_bytes) {
-  return row_bytes >= 128 ? CU_TENSOR_MAP_SWIZZLE_128B
-         : row_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
-         : row_bytes == 32 ? CU_TENSOR_MAP_SWIZZLE_32B
-                           : CU_TENSOR_MAP_SWIZZLE_NONE;
-}
-
 template <typename VolT>
 int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, const rc_layout &lay,
                VolT *pyr, cudaStream_t s) {
-  using S = Stg<VolT>;
   const int N = H * W;
   const int L = lay.num_levels;
   if (L > 4) {
@@ -460,6 +594,7 @@ int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, con
     return RC_EINVAL;
   }
   TcParams p{};
+  p.B = B;
   p.N = N;
   p.MT = ceil_div(N, BM);
   p.nbx = ceil_div(W, TB_W);
@@ -467,17 +602,14 @@ int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, con
   p.KB = ceil_div(D, BK);
   p.num_levels = L;
   p.scale = 1.0f / sqrtf((float)D);
-  p.total_tiles = B * p.MT * p.NT;
   for (int l = 0; l < 4; ++l) {
-    p.Hl[l] = l < L ? lay.H[l] : 0;
-    p.Wl[l] = l < L ? lay.W[l] : 0;
-  }
-  if (L > 3) {
-    p.l3_ptr = pyr + lay.offset[3];
-    p.l3_slab = lay.slab[3];
-    p.l3_pitch = lay.pitch[3];
-    p.l3_H = lay.H[3];
-    p.l3_W = lay.W[3];
+    const bool on = l < L;
+    p.Hl[l] = on ? lay.H[l] : 0;
+    p.Wl[l] = on ? lay.W[l] : 0;
+    p.tiles_y[l] = on ? lay.tiles_y[l] : 0;
+    p.tiles_x[l] = on ? lay.tiles_x[l] : 0;
+    p.slab[l] = on ? lay.slab[l] : 0;
+    p.lvl[l] = on ? (void *)(pyr + lay.offset[l]) : nullptr;
   }
   const long long rows2 = (long long)p.NT * TB_N;
 
@@ -485,7 +617,7 @@ int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, con
   RC_CUDA(cudaGetDevice(&dev));
   RC_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   RC_CUDA(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
-  const size_t fixed = (size_t)p.KB * A_KB_BYTES + 4 * 2 * S::BYTES + 256 + 1024;
+  const size_t fixed = (size_t)p.KB * A_KB_BYTES + 4 * (size_t)stage_bytes_per_warp<VolT>() + 256 + 1024;
   p.stages = 0;
   for (int st = 4; st >= 2; --st)
     if (fixed + (size_t)st * B_ST_BYTES <= (size_t)max_smem) {
@@ -498,7 +630,15 @@ int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, con
   }
   const size_t smem = fixed + (size_t)p.stages * B_ST_BYTES;
 
-  CUtensorMap ma, mb, ml[4];
+  // pairs per group: about two query blocks' worth of tiles per CTA and group
+  const long long tpp = (long long)p.MT * p.NT;
+  long long gp = (2LL * p.NT * sms + tpp - 1) / tpp;
+  if (gp < 1) gp = 1;
+  if (gp > B) gp = B;
+  p.group_pairs = (int)gp;
+  p.num_groups = ceil_div(B, p.group_pairs);
+
+  CUtensorMap ma, mb;
   {
     cuuint64_t dims[3] = {(cuuint64_t)D, (cuuint64_t)N, (cuuint64_t)B};
     cuuint64_t str[2] = {(cuuint64_t)D * 2, (cuuint64_t)N * D * 2};
@@ -513,25 +653,12 @@ int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, con
     int r = encode(&mb, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, f2p, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B, "fmap2");
     if (r) return r;
   }
-  const CUtensorMapDataType odt = sizeof(VolT) == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
-  for (int l = 0; l < 4; ++l) {
-    const int ll = l < L ? l : 0;   // unused maps alias level 0 (never dereferenced)
-    const bool tma_level = (l < L) && (l < 3 || S::L3_TMA);
-    const int lv = tma_level ? l : 0;
-    (void)ll;
-    const int bw = 32 >> lv;
-    cuuint64_t dims[4] = {(cuuint64_t)lay.W[lv], (cuuint64_t)lay.H[lv], (cuuint64_t)N, (cuuint64_t)B};
-    cuuint64_t str[3] = {(cuuint64_t)lay.pitch[lv] * S::ES, (cuuint64_t)lay.slab[lv] * S::ES,
-                         (cuuint64_t)N * lay.slab[lv] * S::ES};
-    cuuint32_t box[4] = {(cuuint32_t)bw, 1, 32, 1};
-    int r = encode(&ml[l], odt, 4, pyr + lay.offset[lv], dims, str, box, swizzle_for(bw * S::ES), "pyramid level");
-    if (r) return r;
-  }
 
   auto kern = build_pyramid_tc_kernel<VolT>;
   RC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  const int grid = p.total_tiles < sms ? p.total_tiles : sms;
-  kern<<<grid, TC_THREADS, smem, s>>>(ma, mb, ml[0], ml[1], ml[2], ml[3], p);
+  const long long group_tiles = (long long)p.group_pairs * tpp;
+  const int grid = group_tiles < sms ? (int)group_tiles : sms;
+  kern<<<grid, TC_THREADS, smem, s>>>(ma, mb, p);
   RC_LAUNCH_CHECK("build_pyramid_tc_kernel");
   return RC_OK;
 }

@@ -49,10 +49,26 @@ struct Levels {
   int num_levels;
   int H[RC_MAX_LEVELS];
   int W[RC_MAX_LEVELS];
-  int pitch[RC_MAX_LEVELS];
+  int tiles_y[RC_MAX_LEVELS];
+  int tiles_x[RC_MAX_LEVELS];
   long long slab[RC_MAX_LEVELS];
   long long offset[RC_MAX_LEVELS];
 };
+
+// Pyramid tiles (rc_layout in raft_corr.h): TILE_H rows of 16 bytes = 64 bytes.
+constexpr int TILE_H = 4;
+template <typename VolT>
+struct Tile {
+  static constexpr int W = 16 / (int)sizeof(VolT);     // elements per 16-byte tile row
+  static constexpr int LOG_W = sizeof(VolT) == 2 ? 3 : 2;
+  static constexpr int ELEMS = TILE_H * W;             // elements per tile
+};
+// element offset of (y, x) inside one query's slab
+template <typename VolT>
+__host__ __device__ inline long long tile_offset(int y, int x, int tiles_x) {
+  return ((long long)(y >> 2) * tiles_x + (x >> Tile<VolT>::LOG_W)) * Tile<VolT>::ELEMS +
+         (y & 3) * Tile<VolT>::W + (x & (Tile<VolT>::W - 1));
+}
 
 inline Levels to_levels(const rc_layout &lay) {
   Levels lv{};
@@ -60,7 +76,8 @@ inline Levels to_levels(const rc_layout &lay) {
   for (int l = 0; l < lay.num_levels; ++l) {
     lv.H[l] = lay.H[l];
     lv.W[l] = lay.W[l];
-    lv.pitch[l] = lay.pitch[l];
+    lv.tiles_y[l] = lay.tiles_y[l];
+    lv.tiles_x[l] = lay.tiles_x[l];
     lv.slab[l] = lay.slab[l];
     lv.offset[l] = lay.offset[l];
   }

@@ -7,15 +7,26 @@
 // Work decomposition: one CTA per strip of 32 consecutive queries of one pair,
 // one warp per pyramid level.  All (2r+1)^2 samples of a query at a level share
 // one fractional offset (ax, ay) and read a (2r+2)^2 window of integer taps
-// (SURVEY 7.0-4), so each warp
-//   1. stages the 32 windows in shared memory with vector loads: 4 (or 3)
-//      lanes cover one 10-tap window row, 8 rows per load instruction, so a
-//      warp-wide load touches ~8 cache lines instead of 32;
-//   2. switches to lane == query: separable interpolation (along x, then y)
-//      out of shared memory (odd row stride -> no bank conflicts) and
-//      128-byte coalesced stores into out[b][channel][q0..q0+31].
+// (SURVEY 7.0-4).  The pyramid is stored in 64-byte tiles of 4 rows x 16 bytes
+// (rc_layout), the unit B200's L2 fetches from HBM, so a window is ~7 tiles.
+//   1. STAGE: the warp copies the 16-byte tile rows ("units") that cover its 32
+//      windows into shared memory, unshifted, with cp.async: unit (row j, tile
+//      column c) of a window is one 16-byte copy of one lane; consecutive lanes
+//      take the units of one window, so the 4 rows of a tile (and its
+//      x-neighbour) sit in the same instruction and coalesce.  All copies of a
+//      warp are in flight at once, none holds a register.  Out-of-map units are
+//      zero-filled (= grid_sample's zeros padding); padding columns inside edge
+//      tiles are zero in memory.
+//   2. INTERPOLATE: lane == query.  The lane reads the units of a window row
+//      with 16-byte shared loads, shifts them by its own sub-tile offset
+//      (x0 mod tile width) in registers, runs the separable interpolation
+//      (along x, then y) and stores 128 bytes per warp and channel straight into
+//      out[b][channel][q0..q0+31].
+// Shared memory holds one row of units per query; the unit position is XORed
+// with bits of the query so that the 16-byte reads of 8 consecutive queries hit
+// 8 different bank groups.
 // HBM-bound: per query and level it reads (2r+2)^2 volume elements and writes
-// (2r+1)^2 floats; no intermediate ever reaches global memory (the reference
+// (2r+1)^2 floats; no intermediate reaches global memory (the reference
 // materialises the sampling grid, four per-level outputs, a cat and a
 // permute().contiguous() copy).
 #include "common.cuh"
@@ -23,36 +34,31 @@
 namespace rc {
 namespace {
 
-template <typename VolT>
-struct Vec4;
-template <>
-struct Vec4<float> {
-  using type = float4;
-  static __device__ __forceinline__ void unpack(const float4 &v, float *f) {
-    f[0] = v.x; f[1] = v.y; f[2] = v.z; f[3] = v.w;
-  }
-  static __device__ __forceinline__ float4 zero() { return make_float4(0.f, 0.f, 0.f, 0.f); }
-};
-template <>
-struct Vec4<__nv_bfloat16> {
-  using type = uint2;
-  static __device__ __forceinline__ void unpack(const uint2 &v, float *f) {
-    f[0] = __uint_as_float(v.x << 16);
-    f[1] = __uint_as_float(v.x & 0xffff0000u);
-    f[2] = __uint_as_float(v.y << 16);
-    f[3] = __uint_as_float(v.y & 0xffff0000u);
-  }
-  static __device__ __forceinline__ uint2 zero() { return make_uint2(0u, 0u); }
-};
-
-template <int R>
+// Geometry of one (volume type, radius) combination.
+template <typename VolT, int R>
 struct Win {
-  static constexpr int NW = 2 * R + 1;        // samples per axis
-  static constexpr int T = 2 * R + 2;         // integer taps per axis
-  static constexpr int VPR = (T + 3 + 3) / 4; // aligned 4-vectors that cover any T-tap row
-  static constexpr int STRIDE = (T * T) | 1;  // words per query in smem (odd)
-  static constexpr int SLOTS = T * VPR;       // vector loads per query
-  static constexpr int U = (SLOTS % 8 == 0) ? 8 : ((SLOTS % 6 == 0) ? 6 : 2);   // loads in flight per lane
+  static constexpr int NW = 2 * R + 1;                 // samples per axis
+  static constexpr int T = 2 * R + 2;                  // integer taps per axis
+  static constexpr int EPV = Tile<VolT>::W;            // elements per 16-byte unit
+  static constexpr int LOG_EPV = Tile<VolT>::LOG_W;
+  static constexpr int SPAN = EPV - 1 + T;             // widest reach from the first unit's start
+  // When the widest window overshoots NCOL units by exactly one element, that
+  // element is fetched by the query's own lane instead of a whole extra unit column.
+  static constexpr int EXTRA = (SPAN % EPV == 1) ? 1 : 0;
+  static constexpr int NCOL = EXTRA ? SPAN / EPV : (SPAN + EPV - 1) / EPV;
+  static constexpr int SL = T * NCOL;                  // units per window
+  static constexpr int ROWW = NCOL * 4;                // 32-bit words per staged window row
+  static constexpr int WPQ = SL * 4;                   // words per window
+  static constexpr int K = SL | 1;                     // odd bank-rotation multiplier
+  static constexpr int ITER = SL / 2;                  // copy rounds per group of 16 queries
+  // staged forward window: units per query row, padded to 4 (mod 8) so that rows of
+  // consecutive queries alternate between the two halves of the 8 bank groups
+  static constexpr int SU = SL + ((4 - SL % 8) + 8) % 8;
+  static constexpr int WIN_BYTES = 32 * SU * 16;       // per level (32 queries)
+  // words of a row a lane may need: NEED, read from W[0 .. NEED+2]
+  static constexpr int NEED = sizeof(VolT) == 2 ? T / 2 + 1 : T;
+  static_assert(SL % 2 == 0, "T is even");
+  static_assert(NEED + 3 <= ROWW + 1, "window row does not fit the staged units");
 };
 
 struct QueryWin {
@@ -77,65 +83,154 @@ __device__ __forceinline__ QueryWin make_window(float x, float y, int level, boo
   return w;
 }
 
-// Stage the T x T windows of the warp's 32 queries into `taps`
-// (taps[qq*STRIDE + j*T + i] = level[y0+j][x0+i], zero outside the map).
+// 16-byte asynchronous copy global -> shared, zero-filled when !ok (src-size 0).
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void *src, bool ok) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(ok ? 16 : 0) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+  asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+}
+// One element as raw bits in the low part of a word (bf16: low half), 0 when !ok.
+template <typename VolT>
+__device__ __forceinline__ uint32_t ldg_elem(const VolT *p, bool ok) {
+  uint32_t v;
+  if (sizeof(VolT) == 2) {
+    unsigned short h;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %2, 0;\n\tmov.b16 %0, 0;\n\t"
+        "@p ld.global.nc.b16 %0, [%1];\n\t}"
+        : "=h"(h) : "l"(p), "r"((int)ok) : "memory");
+    v = h;
+  } else {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %2, 0;\n\tmov.b32 %0, 0;\n\t"
+        "@p ld.global.nc.b32 %0, [%1];\n\t}"
+        : "=r"(v) : "l"(p), "r"((int)ok) : "memory");
+  }
+  return v;
+}
+
+// word index (within a window) -> shared-memory word of query qq
+template <typename W_>
+__device__ __forceinline__ int smem_word(int word, int qq) {
+  return word * 32 + ((qq * W_::K + (word >> 2)) & 31);
+}
+
+// Geometry of one level as the kernels need it.
+struct LevelGeom {
+  int Hl, Wl, tiles_x;
+  long long slab;      // elements per query
+};
+
+// byte offset of unit `slot` of query qq inside a level's staged windows
+template <typename W_>
+__device__ __forceinline__ uint32_t unit_off(int qq, int slot) {
+  return (uint32_t)(qq * W_::SU + (slot ^ ((qq >> 1) & 3))) * 16u;
+}
+
+// STAGE (see the file comment): copy the units of the warp's 32 windows into `win`
+// (shared-memory byte address, W_::WIN_BYTES).  `lvl` points at the level,
+// slab0 = b*N + q0.  Completion: cp_async_wait_all() + __syncwarp().
 template <typename VolT, int R>
-__device__ __forceinline__ void stage_windows(const VolT *__restrict__ lvl, float *taps,
-                                              const QueryWin &w, long long slab0, long long slab,
-                                              int pitch, int Hl, int Wl, int lane) {
-  using W_ = Win<R>;
-  using V = Vec4<VolT>;
-  constexpr int U = W_::U;
-  static_assert(W_::SLOTS % U == 0, "unroll must divide slots");
+__device__ __forceinline__ void stage_windows(const VolT *__restrict__ lvl, uint32_t win, const QueryWin &w,
+                                              long long slab0, const LevelGeom &g, int lane) {
+  using W_ = Win<VolT, R>;
 #pragma unroll 1
-  for (int it0 = 0; it0 < W_::SLOTS; it0 += U) {
-    typename V::type v[U];
-    int dst[U], xb[U], qx0[U];
+  for (int grp = 0; grp < 2; ++grp) {
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int s = (it0 + u) * 32 + lane;
-      const int qq = s / W_::SLOTS;
-      const int rem = s - qq * W_::SLOTS;
-      const int j = rem / W_::VPR;
-      const int k = rem - j * W_::VPR;
+    for (int it = 0; it < W_::ITER; ++it) {
+      const int s = it * 32 + lane;                 // 0 .. 16*SL-1
+      const int ql = s / W_::SL;                    // query within the group
+      const int slot = s - ql * W_::SL;             // unit within the window: j * NCOL + c
+      const int j = slot / W_::NCOL;
+      const int c = slot - j * W_::NCOL;
+      const int qq = grp * 16 + ql;
       const int x0 = __shfl_sync(0xffffffffu, w.x0, qq);
       const int y0 = __shfl_sync(0xffffffffu, w.y0, qq);
       const int y = y0 + j;
-      const int xbase = ((x0 >> 2) + k) * 4;
-      const bool ok = y >= 0 && y < Hl && xbase >= 0 && xbase < pitch;
-      v[u] = V::zero();
-      if (ok) {
-        const VolT *p = lvl + (slab0 + qq) * slab + (size_t)y * pitch + xbase;
-        v[u] = __ldg(reinterpret_cast<const typename V::type *>(p));
-      }
-      dst[u] = qq * W_::STRIDE + j * W_::T;
-      xb[u] = xbase;
-      qx0[u] = x0;
-    }
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      float f[4];
-      V::unpack(v[u], f);
-#pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const int x = xb[u] + e;
-        const int i = x - qx0[u];
-        if (i >= 0 && i < W_::T) taps[dst[u] + i] = (x < Wl) ? f[e] : 0.f;
-      }
+      const int tc = (x0 >> W_::LOG_EPV) + c;
+      const bool ok = (unsigned)y < (unsigned)g.Hl && (unsigned)tc < (unsigned)g.tiles_x;
+      const long long unit = ((long long)(y >> 2) * g.tiles_x + tc) * 4 + (y & 3);
+      const VolT *p = lvl + (slab0 + qq) * g.slab + unit * W_::EPV;
+      cp_async16(win + unit_off<W_>(qq, slot), ok ? p : lvl, ok);
     }
   }
 }
 
-// grid: B * ceil(N/32) strips; block: 32 * num_levels threads; dyn smem: L*32*STRIDE floats
+// The one element a widest window needs beyond its NCOL units, per window row
+// (raw bits; zero when this query does not need it or it lies outside the map).
+template <typename VolT, int R>
+__device__ __forceinline__ void load_extras(const VolT *__restrict__ lvl, const QueryWin &w, long long slab_q,
+                                            const LevelGeom &g, uint32_t (&ex)[Win<VolT, R>::T]) {
+  using W_ = Win<VolT, R>;
+  if (W_::EXTRA) {
+    const bool need = (w.x0 & (W_::EPV - 1)) == W_::EPV - 1;
+    const int tc = (w.x0 >> W_::LOG_EPV) + W_::NCOL;
+#pragma unroll
+    for (int j = 0; j < W_::T; ++j) {
+      const int y = w.y0 + j;
+      const bool ok = need && (unsigned)y < (unsigned)g.Hl && (unsigned)tc < (unsigned)g.tiles_x;
+      const long long unit = ((long long)(y >> 2) * g.tiles_x + tc) * 4 + (y & 3);
+      ex[j] = ldg_elem<VolT>(lvl + slab_q * g.slab + unit * W_::EPV, ok);
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < W_::T; ++j) ex[j] = 0u;
+  }
+}
+
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+  return v;
+}
+
+// Row j of this lane's window as T floats, out of the staged units: read the
+// row's NCOL units, shift by the lane's sub-tile offset o in registers.
+template <typename VolT, int R>
+__device__ __forceinline__ void read_row(uint32_t win, int lane, int j, int o, uint32_t extra,
+                                         float (&v)[Win<VolT, R>::T]) {
+  using W_ = Win<VolT, R>;
+  constexpr int T = W_::T, NEED = W_::NEED;
+  uint32_t wv[W_::ROWW + 3];
+#pragma unroll
+  for (int c = 0; c < W_::NCOL; ++c) {
+    const uint4 u = lds128(win + unit_off<W_>(lane, j * W_::NCOL + c));
+    wv[4 * c + 0] = u.x; wv[4 * c + 1] = u.y; wv[4 * c + 2] = u.z; wv[4 * c + 3] = u.w;
+  }
+  wv[W_::ROWW] = extra;
+  wv[W_::ROWW + 1] = 0u;
+  wv[W_::ROWW + 2] = 0u;
+  const int m = sizeof(VolT) == 2 ? (o >> 1) : o;     // word shift, 0..3
+  uint32_t xs[NEED + 2], ys[NEED];
+#pragma unroll
+  for (int k = 0; k < NEED + 2; ++k) xs[k] = (m & 1) ? wv[k + 1] : wv[k];
+#pragma unroll
+  for (int k = 0; k < NEED; ++k) ys[k] = (m & 2) ? xs[k + 2] : xs[k];
+  if (sizeof(VolT) == 2) {
+    const int sh = (o & 1) * 16;
+#pragma unroll
+    for (int k = 0; k < T / 2; ++k) {
+      const uint32_t pr = __funnelshift_r(ys[k], ys[k + 1], sh);
+      v[2 * k] = __uint_as_float(pr << 16);
+      v[2 * k + 1] = __uint_as_float(pr & 0xffff0000u);
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < T; ++i) v[i] = __uint_as_float(ys[i]);
+  }
+}
+
+// grid: B * ceil(N/32) strips; block: 32 * num_levels threads; dyn smem: L * WIN_BYTES
 template <typename VolT, int R>
 __global__ void __launch_bounds__(32 * RC_MAX_LEVELS)
 lookup_fwd_kernel(const VolT *__restrict__ pyr, const float *__restrict__ coords,
                   float *__restrict__ out, Levels lv, int N, int strips_per_pair) {
-  using W_ = Win<R>;
-  extern __shared__ float smem[];
+  using W_ = Win<VolT, R>;
+  extern __shared__ __align__(16) uint32_t smem_u[];
   const int lane = threadIdx.x & 31;
   const int l = threadIdx.x >> 5;
-  float *taps = smem + (size_t)l * 32 * W_::STRIDE;
+  const uint32_t win = (uint32_t)__cvta_generic_to_shared(smem_u) + l * W_::WIN_BYTES;
 
   const int b = blockIdx.x / strips_per_pair;
   const int q0 = (blockIdx.x - b * strips_per_pair) * 32;
@@ -147,50 +242,66 @@ lookup_fwd_kernel(const VolT *__restrict__ pyr, const float *__restrict__ coords
     y = __ldg(coords + ((size_t)b * 2 + 1) * N + q);
   }
   const QueryWin w = make_window<R>(x, y, l, active);
+  LevelGeom g;
+  g.Hl = lv.H[l]; g.Wl = lv.W[l]; g.tiles_x = lv.tiles_x[l]; g.slab = lv.slab[l];
+  const VolT *lvl = pyr + lv.offset[l];
+  const long long slab0 = (long long)b * N + q0;
 
-  stage_windows<VolT, R>(pyr + lv.offset[l], taps, w, (long long)b * N + q0, lv.slab[l],
-                         lv.pitch[l], lv.H[l], lv.W[l], lane);
+  uint32_t ex[W_::T];
+  stage_windows<VolT, R>(lvl, win, w, slab0, g, lane);
+  load_extras<VolT, R>(lvl, w, slab0 + lane, g, ex);
+  cp_async_wait_all();
   __syncwarp();
 
   if (!active) return;
-  const float *t = taps + lane * W_::STRIDE;
+  const int o = w.x0 & (W_::EPV - 1);
   const int C = lv.num_levels * W_::NW * W_::NW;
-  float *o = out + ((size_t)b * C + (size_t)l * W_::NW * W_::NW) * N + q;
+  float *op = out + ((size_t)b * C + (size_t)l * W_::NW * W_::NW) * N + q;
   float hprev[W_::NW];
 #pragma unroll
   for (int j = 0; j < W_::T; ++j) {
     float v[W_::T], h[W_::NW];
-#pragma unroll
-    for (int i = 0; i < W_::T; ++i) v[i] = t[j * W_::T + i];
+    read_row<VolT, R>(win, lane, j, o, ex[j], v);
 #pragma unroll
     for (int i = 0; i < W_::NW; ++i) h[i] = fmaf(w.ax, v[i + 1] - v[i], v[i]);
     if (j > 0) {
 #pragma unroll
       for (int i = 0; i < W_::NW; ++i)
-        o[(size_t)(i * W_::NW + (j - 1)) * N] = fmaf(w.ay, h[i] - hprev[i], hprev[i]);
+        op[(size_t)(i * W_::NW + (j - 1)) * N] = fmaf(w.ay, h[i] - hprev[i], hprev[i]);
     }
 #pragma unroll
     for (int i = 0; i < W_::NW; ++i) hprev[i] = h[i];
   }
 }
 
-// Backward.  Same decomposition.  Per warp: stage the forward windows (needed
-// for d/dcoords), then lane == query folds the (2r+1)^2 output gradients into
-// the (2r+2)^2 tap gradients IN PLACE in shared memory (row j of the window is
-// dead once output rows j-1 and j have used it), then the staging pattern is
-// run in reverse to add the tap gradients into the fp32 gradient pyramid.
-// Every query owns its slabs, so the read-modify-write needs no atomics.
+// Backward.  Same decomposition, one warp per level.
+//   A. (only if d/dcoords is wanted) stage the forward windows as in the forward.
+//   B. lane == query: fold the (2r+1)^2 output gradients into the (2r+2)^2 tap
+//      gradients (separable, gather form) and park them in shared memory in the
+//      unshifted unit layout of the fp32 GRADIENT pyramid; accumulate d/dcoords
+//      from the forward taps on the way.
+//   C. lane == unit: add the units into the gradient pyramid with 16-byte vector
+//      reductions (red.global.add.v4.f32).  Every query owns its slabs, so each
+//      address is hit once per launch; words of a unit outside the window (never
+//      written in B) and padding columns are masked out.
 template <typename VolT, int R>
 __global__ void __launch_bounds__(32 * RC_MAX_LEVELS)
 lookup_bwd_kernel(const VolT *__restrict__ pyr, const float *__restrict__ coords,
                   const float *__restrict__ grad_out, float *__restrict__ gpyr,
                   float *__restrict__ gcoords, Levels lv, Levels glv, int N, int strips_per_pair) {
-  using W_ = Win<R>;
-  extern __shared__ float smem[];
+  using W_ = Win<VolT, R>;     // forward window in the volume's layout
+  using G_ = Win<float, R>;    // tap gradients in the fp32 gradient pyramid's layout
+  constexpr int T = W_::T, NW = W_::NW;
+  extern __shared__ __align__(16) uint32_t smem_u[];
   __shared__ float dc[RC_MAX_LEVELS][2][32];
   const int lane = threadIdx.x & 31;
   const int l = threadIdx.x >> 5;
-  float *taps = smem + (size_t)l * 32 * W_::STRIDE;
+  const bool want_dc = gcoords != nullptr;
+  const bool want_vol = gpyr != nullptr;
+  const int gwin_words = want_vol ? 32 * G_::WPQ : 0;
+  const int per_level = gwin_words + (want_dc ? W_::WIN_BYTES / 4 : 0);     // words
+  uint32_t *gwin = smem_u + (size_t)l * per_level;
+  const uint32_t win = (uint32_t)__cvta_generic_to_shared(gwin + gwin_words);
 
   const int b = blockIdx.x / strips_per_pair;
   const int q0 = (blockIdx.x - b * strips_per_pair) * 32;
@@ -202,92 +313,127 @@ lookup_bwd_kernel(const VolT *__restrict__ pyr, const float *__restrict__ coords
     y = __ldg(coords + ((size_t)b * 2 + 1) * N + q);
   }
   const QueryWin w = make_window<R>(x, y, l, active);
-  const bool want_dc = gcoords != nullptr;
+  const long long slab0 = (long long)b * N + q0;
 
+  uint32_t ex[T];
+#pragma unroll
+  for (int j = 0; j < T; ++j) ex[j] = 0u;
   if (want_dc) {
-    stage_windows<VolT, R>(pyr + lv.offset[l], taps, w, (long long)b * N + q0, lv.slab[l],
-                           lv.pitch[l], lv.H[l], lv.W[l], lane);
+    LevelGeom g;
+    g.Hl = lv.H[l]; g.Wl = lv.W[l]; g.tiles_x = lv.tiles_x[l]; g.slab = lv.slab[l];
+    const VolT *lvl = pyr + lv.offset[l];
+    stage_windows<VolT, R>(lvl, win, w, slab0, g, lane);
+    load_extras<VolT, R>(lvl, w, slab0 + lane, g, ex);
+    cp_async_wait_all();
     __syncwarp();
   }
 
+  LevelGeom gg;
+  gg.Hl = glv.H[l]; gg.Wl = glv.W[l]; gg.tiles_x = glv.tiles_x[l]; gg.slab = glv.slab[l];
+  float *glvl = want_vol ? gpyr + glv.offset[l] : nullptr;
+
+  // ---- B
   float dx = 0.f, dy = 0.f;
   {
-    float *t = taps + lane * W_::STRIDE;
-    const int C = lv.num_levels * W_::NW * W_::NW;
-    const float *g = grad_out + ((size_t)b * C + (size_t)l * W_::NW * W_::NW) * N + q;
-    float hg_prev[W_::T];   // x-folded gradient of output row j-1
-    float cur[W_::T];       // forward taps, row j
+    const int o = w.x0 & (W_::EPV - 1);
+    const int og = w.x0 & (G_::EPV - 1);
+    const int C = lv.num_levels * NW * NW;
+    const float *gp = grad_out + ((size_t)b * C + (size_t)l * NW * NW) * N + q;
+    float hg_prev[T];   // x-folded gradient of output row j-1
+    float cur[T];       // forward taps, row j
 #pragma unroll
-    for (int i = 0; i < W_::T; ++i) {
-      hg_prev[i] = 0.f;
-      cur[i] = want_dc ? t[i] : 0.f;
+    for (int i = 0; i < T; ++i) { hg_prev[i] = 0.f; cur[i] = 0.f; }
+    if (want_dc) read_row<VolT, R>(win, lane, 0, o, ex[0], cur);
+#pragma unroll
+    for (int j = 0; j <= NW; ++j) {
+      float trow[T];    // tap-gradient row j
+      if (j < NW) {
+        float gj[NW], hg[T];
+#pragma unroll
+        for (int i = 0; i < NW; ++i) gj[i] = active ? __ldg(gp + (size_t)(i * NW + j) * N) : 0.f;
+        if (want_dc) {
+          float nxt[T];
+          read_row<VolT, R>(win, lane, j + 1, o, ex[j + 1], nxt);
+#pragma unroll
+          for (int i = 0; i < NW; ++i) {
+            const float d0 = cur[i + 1] - cur[i], d1 = nxt[i + 1] - nxt[i];
+            dx = fmaf(gj[i], fmaf(w.ay, d1 - d0, d0), dx);
+            const float e0 = nxt[i] - cur[i], e1 = nxt[i + 1] - cur[i + 1];
+            dy = fmaf(gj[i], fmaf(w.ax, e1 - e0, e0), dy);
+          }
+#pragma unroll
+          for (int i = 0; i < T; ++i) cur[i] = nxt[i];
+        }
+        // fold along x: hg[ii] = (1-ax) g[ii] + ax g[ii-1]
+#pragma unroll
+        for (int i = 0; i < T; ++i) {
+          const float a = (i < NW) ? gj[i] : 0.f;
+          const float c = (i > 0) ? gj[i - 1] : 0.f;
+          hg[i] = fmaf(w.ax, c - a, a);
+        }
+        // tap-gradient row j is final: (1-ay) hg_j + ay hg_{j-1}
+#pragma unroll
+        for (int i = 0; i < T; ++i) {
+          trow[i] = fmaf(w.ay, hg_prev[i] - hg[i], hg[i]);
+          hg_prev[i] = hg[i];
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < T; ++i) trow[i] = w.ay * hg_prev[i];
+      }
+      if (want_vol) {
+#pragma unroll
+        for (int i = 0; i < T; ++i) {
+          if (og + i < G_::ROWW) {
+            gwin[smem_word<G_>(j * G_::ROWW + og + i, lane)] = __float_as_uint(trow[i]);
+          } else {
+            // the one tap beyond the staged units (og == 3, last tap): this lane owns it
+            const int yy = w.y0 + j, xx = w.x0 + i;
+            if (active && (unsigned)yy < (unsigned)gg.Hl && (unsigned)xx < (unsigned)gg.Wl)
+              atomicAdd(glvl + (slab0 + lane) * gg.slab + tile_offset<float>(yy, xx, gg.tiles_x), trow[i]);
+          }
+        }
+      }
     }
-#pragma unroll
-    for (int j = 0; j < W_::NW; ++j) {
-      float gj[W_::NW], nxt[W_::T], hg[W_::T];
-#pragma unroll
-      for (int i = 0; i < W_::NW; ++i) gj[i] = active ? __ldg(g + (size_t)(i * W_::NW + j) * N) : 0.f;
-#pragma unroll
-      for (int i = 0; i < W_::T; ++i) nxt[i] = want_dc ? t[(j + 1) * W_::T + i] : 0.f;
-      // d/dcoords
-#pragma unroll
-      for (int i = 0; i < W_::NW; ++i) {
-        const float d0 = cur[i + 1] - cur[i], d1 = nxt[i + 1] - nxt[i];
-        dx = fmaf(gj[i], fmaf(w.ay, d1 - d0, d0), dx);
-        const float e0 = nxt[i] - cur[i], e1 = nxt[i + 1] - cur[i + 1];
-        dy = fmaf(gj[i], fmaf(w.ax, e1 - e0, e0), dy);
-      }
-      // fold along x: hg[ii] = (1-ax) g[ii] + ax g[ii-1]
-#pragma unroll
-      for (int i = 0; i < W_::T; ++i) {
-        const float a = (i < W_::NW) ? gj[i] : 0.f;
-        const float c = (i > 0) ? gj[i - 1] : 0.f;
-        hg[i] = fmaf(w.ax, c - a, a);
-      }
-      // tap-gradient row j is final: (1-ay) hg_j + ay hg_{j-1}
-#pragma unroll
-      for (int i = 0; i < W_::T; ++i) t[j * W_::T + i] = fmaf(w.ay, hg_prev[i] - hg[i], hg[i]);
-#pragma unroll
-      for (int i = 0; i < W_::T; ++i) {
-        hg_prev[i] = hg[i];
-        cur[i] = nxt[i];
-      }
-    }
-#pragma unroll
-    for (int i = 0; i < W_::T; ++i) t[(W_::T - 1) * W_::T + i] = w.ay * hg_prev[i];
   }
   __syncwarp();
 
-  if (gpyr != nullptr) {
-    float *glvl = gpyr + glv.offset[l];
-    const long long slab0 = (long long)b * N + q0;
-    const int Hl = glv.H[l], Wl = glv.W[l], pitch = glv.pitch[l];
-    const long long slab = glv.slab[l];
-#pragma unroll 4
-    for (int it = 0; it < W_::SLOTS; ++it) {
-      const int s = it * 32 + lane;
-      const int qq = s / W_::SLOTS;
-      const int rem = s - qq * W_::SLOTS;
-      const int j = rem / W_::VPR;
-      const int k = rem - j * W_::VPR;
-      const int x0 = __shfl_sync(0xffffffffu, w.x0, qq);
-      const int y0 = __shfl_sync(0xffffffffu, w.y0, qq);
-      const int yy = y0 + j;
-      const int xbase = ((x0 >> 2) + k) * 4;
-      // touch the vector only if it intersects the window and the map
-      const bool ok = yy >= 0 && yy < Hl && xbase >= 0 && xbase < pitch && xbase < Wl &&
-                      xbase + 3 >= x0 && xbase < x0 + W_::T;
-      if (ok) {
-        float4 *p = reinterpret_cast<float4 *>(glvl + (slab0 + qq) * slab + (size_t)yy * pitch + xbase);
-        float4 v = *p;
-        float f[4] = {v.x, v.y, v.z, v.w};
+  // ---- C
+  if (want_vol) {
+#pragma unroll 1
+    for (int grp = 0; grp < 2; ++grp) {
+#pragma unroll 5
+      for (int it = 0; it < G_::ITER; ++it) {
+        const int s = it * 32 + lane;
+        const int ql = s / G_::SL;
+        const int slot = s - ql * G_::SL;
+        const int j = slot / G_::NCOL;
+        const int c = slot - j * G_::NCOL;
+        const int qq = grp * 16 + ql;
+        const int x0 = __shfl_sync(0xffffffffu, w.x0, qq);
+        const int y0 = __shfl_sync(0xffffffffu, w.y0, qq);
+        const int yy = y0 + j;
+        const int tc = (x0 >> G_::LOG_EPV) + c;
+        const bool ok = (unsigned)yy < (unsigned)gg.Hl && (unsigned)tc < (unsigned)gg.tiles_x;
+        const long long unit = ((long long)(yy >> 2) * gg.tiles_x + tc) * 4 + (yy & 3);
+        float *ptr = glvl + (slab0 + qq) * gg.slab + unit * G_::EPV;
+        const int base = (slot * 4) * 32 + ((qq * G_::K + slot) & 31);
+        const int xb = tc * G_::EPV;          // x of the unit's first element
+        const int i0 = xb - x0;               // window index of that element
+        float f[4];
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
-          const int xx = xbase + e;
-          const int i = xx - x0;
-          if (i >= 0 && i < W_::T && xx < Wl) f[e] += taps[qq * W_::STRIDE + j * W_::T + i];
+          const int i = i0 + e;
+          const bool in = i >= 0 && i < T && xb + e < gg.Wl;
+          f[e] = in ? __uint_as_float(gwin[base + 32 * e]) : 0.f;
         }
-        *p = make_float4(f[0], f[1], f[2], f[3]);
+        // one 16-byte reduction per unit: performed at L2, nothing comes back, so
+        // no load latency sits on the warp.  Each address is touched once per
+        // launch (a query owns its slabs): the result does not depend on order.
+        if (ok)
+          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(ptr), "f"(f[0]), "f"(f[1]), "f"(f[2]),
+                       "f"(f[3])
+                       : "memory");
       }
     }
   }
@@ -312,10 +458,10 @@ lookup_bwd_kernel(const VolT *__restrict__ pyr, const float *__restrict__ coords
 template <typename VolT, int R>
 int lookup_fwd_t(const VolT *pyr, const float *coords, const rc_layout &lay, float *out,
                  cudaStream_t s) {
-  using W_ = Win<R>;
+  using W_ = Win<VolT, R>;
   const int N = lay.N;
   const int strips = ceil_div(N, 32);
-  const size_t smem = (size_t)lay.num_levels * 32 * W_::STRIDE * sizeof(float);
+  const size_t smem = (size_t)lay.num_levels * W_::WIN_BYTES;
   auto kern = lookup_fwd_kernel<VolT, R>;
   RC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   kern<<<lay.B * strips, 32 * lay.num_levels, smem, s>>>(pyr, coords, out, to_levels(lay), N, strips);
@@ -326,10 +472,12 @@ int lookup_fwd_t(const VolT *pyr, const float *coords, const rc_layout &lay, flo
 template <typename VolT, int R>
 int lookup_bwd_t(const VolT *pyr, const float *coords, const float *grad_out, const rc_layout &lay,
                  const rc_layout &glay, float *gpyr, float *gcoords, cudaStream_t s) {
-  using W_ = Win<R>;
+  using W_ = Win<VolT, R>;
+  using G_ = Win<float, R>;
   const int N = lay.N;
   const int strips = ceil_div(N, 32);
-  const size_t smem = (size_t)lay.num_levels * 32 * W_::STRIDE * sizeof(float);
+  const size_t per_level = (gpyr ? (size_t)32 * G_::WPQ * 4 : 0) + (gcoords ? (size_t)W_::WIN_BYTES : 0);
+  const size_t smem = (size_t)lay.num_levels * per_level;
   auto kern = lookup_bwd_kernel<VolT, R>;
   RC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   kern<<<lay.B * strips, 32 * lay.num_levels, smem, s>>>(pyr, coords, grad_out, gpyr, gcoords,

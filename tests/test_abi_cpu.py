@@ -33,12 +33,16 @@ def test_abi_version_and_layout():
     lay = _lib.pyramid_layout(1, 55, 128, 4, _lib.RC_VOL_BF16)
     assert list(lay.H)[:4] == [55, 27, 13, 6] and list(lay.W)[:4] == [128, 64, 32, 16]
     assert lay.N == 7040 and lay.elem_bytes == 2
-    # 65 331 200 pyramid elements per Sintel pair (no padding needed at this shape)
-    assert lay.total_elems == 65331200
+    # 64-byte tiles of 4 rows x 8 bf16: 55x128 -> 14x16 tiles, 27x64 -> 7x8, 13x32 -> 4x4, 6x16 -> 2x2
+    assert (lay.tile_h, lay.tile_w) == (4, 8)
+    assert list(lay.tiles_y)[:4] == [14, 7, 4, 2] and list(lay.tiles_x)[:4] == [16, 8, 4, 2]
+    # SURVEY 8 counts 65 331 200 unpadded elements per Sintel pair; tile padding adds 3.4 %
+    assert lay.total_elems == 7040 * 32 * (14 * 16 + 7 * 8 + 4 * 4 + 2 * 2)
     lay = _lib.pyramid_layout(10, 46, 62, 4, _lib.RC_VOL_F32)
-    assert list(lay.W)[:4] == [62, 31, 15, 7] and list(lay.pitch)[:4] == [64, 32, 16, 8]
+    assert (lay.tile_h, lay.tile_w) == (4, 4)
+    assert list(lay.W)[:4] == [62, 31, 15, 7] and list(lay.tiles_x)[:4] == [16, 8, 4, 2]
     for l in range(4):
-        assert lay.slab[l] == lay.H[l] * lay.pitch[l] and lay.offset[l] % 64 == 0
+        assert lay.slab[l] == lay.tiles_y[l] * lay.tiles_x[l] * 16 and lay.offset[l] % 64 == 0
 
 
 def test_layout_rejects_bad_arguments():
@@ -75,3 +79,23 @@ def test_product_does_not_import_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 src = open(os.path.join(dirpath, f)).read()
                 assert "oracle" not in src, f"{f} mentions the oracle"
+
+
+def test_level_view_inverts_the_tile_layout():
+    """level_view (what corr_pyramid and the GPU tests read levels through) against
+    the element address formula of rc_layout in include/raft_corr.h."""
+    import torch
+    for vol, shape in ((_lib.RC_VOL_BF16, (2, 13, 21)), (_lib.RC_VOL_F32, (1, 9, 10))):
+        B, H, W = shape
+        lay = _lib.pyramid_layout(B, H, W, 2, vol)
+        buf = torch.arange(int(lay.total_elems), dtype=torch.float32)
+        th, tw = lay.tile_h, lay.tile_w
+        for l in range(2):
+            v = _lib.level_view(buf, lay, l)
+            assert tuple(v.shape) == (B * H * W, lay.H[l], lay.W[l])
+            for (q, y, x) in ((0, 0, 0), (B * H * W - 1, lay.H[l] - 1, lay.W[l] - 1), (7, 3, 4), (5, 4, 3)):
+                if y >= lay.H[l] or x >= lay.W[l]:
+                    continue
+                want = (lay.offset[l] + q * lay.slab[l] + ((y // th) * lay.tiles_x[l] + x // tw) * th * tw
+                        + (y % th) * tw + x % tw)
+                assert int(v[q, y, x]) == want

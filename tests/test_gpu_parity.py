@@ -79,7 +79,8 @@ def test_build_tensor_core_matches_reference(golden, storage):
         rel_close(v[:, 0].float().cpu().numpy(), pyr[l], tol, f"bf16-exact/{storage} level {l}")
 
 
-@pytest.mark.parametrize("shape", [(1, 256, 55, 128), (2, 128, 46, 62), (1, 64, 17, 33), (3, 32, 8, 9)])
+@pytest.mark.parametrize("shape", [(1, 256, 55, 128), (2, 128, 46, 62), (1, 64, 17, 33), (3, 32, 8, 9), (2, 32, 24, 30),
+                                   (1, 32, 9, 240)])
 @pytest.mark.parametrize("storage", ["bf16", "fp32"])
 def test_build_tensor_core_vs_oracle_shapes(shape, storage):
     B, D, H, W = shape
@@ -97,6 +98,26 @@ def test_build_tensor_core_vs_oracle_shapes(shape, storage):
     for l, v in enumerate(blk.corr_pyramid):
         rel_close(v[:, 0].float().cpu().numpy(), ref[l], 1e-2, f"shape {shape} {storage} level {l} vs fp32",
                   floor=bf16_floor(f1, f2))
+
+
+@pytest.mark.parametrize("math", ["bf16", "fp32"])
+@pytest.mark.parametrize("storage", ["bf16", "fp32"])
+def test_padding_columns_of_edge_tiles_are_zero(storage, math):
+    """rc_layout's invariant: inside rows < H_l, tile columns >= W_l hold zeros
+    (the lookup reads whole 16-byte tile rows and does not mask columns)."""
+    from raft_stir_b200 import _lib
+    rng = np.random.default_rng(11)
+    for shape in ((2, 32, 24, 30), (1, 16, 46, 62), (1, 16, 17, 33)):
+        B, D, H, W = shape
+        blk = R.CorrBlock(t(rng.standard_normal(shape).astype(np.float32)),
+                          t(rng.standard_normal(shape).astype(np.float32)), 4, 4, storage=storage, math=math)
+        for l in range(4):
+            v = _lib._tiled(blk._buf, blk.layout, l)
+            q, ty, th, tx, tw = v.shape
+            full = v.reshape(q, ty * th, tx * tw).float()
+            Hl, Wl = blk.layout.H[l], blk.layout.W[l]
+            assert torch.isfinite(full[:, :Hl]).all(), f"{shape} level {l}"
+            assert not full[:, :Hl, Wl:].any().item(), f"{shape} {storage}/{math} level {l}: nonzero padding columns"
 
 
 def test_build_fp32_vs_oracle_ragged():
@@ -148,7 +169,7 @@ def test_lookup_isolated_from_build(radius, storage):
     pyr = []
     for l, v in enumerate(blk.corr_pyramid):
         vals = torch.from_numpy(rng.standard_normal(tuple(v.shape)).astype(np.float32)).to(v.dtype)
-        v.copy_(vals.to(dev()))
+        _lib.level_store(blk._buf, blk.layout, l, vals[:, 0])
         pyr.append(vals.float().numpy()[:, 0])
     coords = (O.coords_grid(B, H, W) + rng.normal(0, 6, (B, 2, H, W))).astype(np.float32)
     out = blk(t(coords)).cpu().numpy()
@@ -198,7 +219,7 @@ def test_lookup_backward_grad_pyramid(golden):
                                             B, H, W, 4, r, gbuf.data_ptr(), None,
                                             torch.cuda.current_stream().cuda_stream), "rc_lookup_bwd")
     for l in range(4):
-        v = torch.as_strided(gbuf, (B * H * W, glay.H[l], glay.W[l]), (glay.slab[l], glay.pitch[l], 1), int(glay.offset[l]))
+        v = _lib.level_view(gbuf, glay, l)
         got = v.cpu().numpy() / 2.0
         if l == 0:
             rel_close(got.sum(axis=2), golden["dpyr0_rowsum"], 1e-4, "dpyr0 row sums")

@@ -38,11 +38,7 @@ def _build_both(f1, f2, L, vol_dtype):
     _lib.check(lib.rc_build_pyramid_static(f1.data_ptr(), f2.data_ptr(), B, D, H, W, L, vol_dtype,
                                            got.data_ptr(), stream), "rc_build_pyramid_static")
     torch.cuda.synchronize()
-    views = []
-    for buf in (ref, got):
-        views.append([torch.as_strided(buf, (B * lay.N, lay.H[l], lay.W[l]), (lay.slab[l], lay.pitch[l], 1),
-                                       int(lay.offset[l])).float() for l in range(L)])
-    return views
+    return [[_lib.level_view(buf, lay, l).float() for l in range(L)] for buf in (ref, got)]
 
 
 def test_static_scratch_build_matches_workspace_build_twice():
