@@ -42,42 +42,53 @@ constexpr int EPI_WARP0 = 2;
 struct TcParams {
   int B, N, MT, NT, nbx, KB, num_levels, stages;
   int group_pairs, num_groups;      // pairs processed together (see TileWalk)
-  float scale;
+  float scale;                      // what is left of 1/sqrt(D) after the pack's exact power-of-two part
   // pyramid geometry (levels >= num_levels are unused)
   int Hl[4], Wl[4], tiles_y[4], tiles_x[4];
   long long slab[4];                // elements per query
   void *lvl[4];                     // base pointer of each level
 };
 
-// Order in which a CTA visits (pair, query block, target block) tiles.  Pairs are
-// taken in groups of `group_pairs`; inside a group every CTA gets one contiguous
-// range of the group's tiles (balanced to within one tile, and a range stays on
-// one query block for NT tiles so the A operand is reloaded rarely).  Grouping
-// keeps the packed fmap2 of only a few pairs hot in L2 next to the output stream;
-// one range over all pairs has every pair's operand in flight at once and misses.
+// Order in which a CTA visits (pair b, query block m, target block n) tiles.
+// Pairs are taken in groups of `group_pairs`; inside a group every CTA gets one
+// contiguous range of the group's tiles in (b, m, n) order (balanced to within
+// one tile; a range stays on one query block for NT tiles, so the A operand is
+// reloaded rarely).  Grouping keeps the packed fmap2 of only a few pairs hot in
+// L2 next to the output stream; one range over all pairs has every pair's
+// operand in flight at once and misses.  Divisions happen once per range.
 struct TileWalk {
-  int grp;
-  long long t, t_end, base;
-  __device__ __forceinline__ void init() { grp = -1; t = 0; t_end = 0; base = 0; }
-  // next global tile index ((b * MT + m) * NT + n), or false when done
-  __device__ __forceinline__ bool next(const TcParams &p, long long &gt) {
-    while (t >= t_end) {
+  int grp, left;              // current group, tiles left in this CTA's range of it
+  int b, m, n, by, bx;        // the next tile; (by, bx) = n's block coordinates
+  __device__ __forceinline__ void init() { grp = -1; left = 0; b = m = n = by = bx = 0; }
+  __device__ __forceinline__ bool next(const TcParams &p, int &ob, int &om, int &on, int &oby, int &obx) {
+    while (left == 0) {
       ++grp;
       if (grp >= p.num_groups) return false;
       const int pair0 = grp * p.group_pairs;
       const int np = min(p.group_pairs, p.B - pair0);
-      const long long tpp = (long long)p.MT * p.NT;
-      const long long tot = np * tpp;
-      t = tot * blockIdx.x / gridDim.x;
-      t_end = tot * (blockIdx.x + 1) / gridDim.x;
-      base = pair0 * tpp;
+      const int tpp = p.MT * p.NT;
+      const long long tot = (long long)np * tpp;
+      const int t0 = (int)(tot * blockIdx.x / gridDim.x);
+      const int t1 = (int)(tot * (blockIdx.x + 1) / gridDim.x);
+      left = t1 - t0;
+      const int pb = t0 / tpp, r = t0 - pb * tpp;
+      b = pair0 + pb;
+      m = r / p.NT;
+      n = r - m * p.NT;
+      by = n / p.nbx;
+      bx = n - by * p.nbx;
     }
-    gt = base + t;
-    ++t;
+    ob = b; om = m; on = n; oby = by; obx = bx;
+    --left;
+    if (++bx == p.nbx) { bx = 0; ++by; }
+    if (++n == p.NT) {
+      n = 0; by = 0; bx = 0;
+      if (++m == p.MT) { m = 0; ++b; }
+    }
     return true;
   }
-  // is `gt` the last tile of this CTA's current range?
-  __device__ __forceinline__ bool range_ends() const { return t >= t_end; }
+  // after next(): does the following tile of this CTA use another A operand (or is there none)?
+  __device__ __forceinline__ bool a_changes(int cb, int cm) const { return left == 0 || b != cb || m != cm; }
 };
 
 // ---------------------------------------------------------------- PTX wrappers
@@ -122,19 +133,6 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *map
       ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
       : "memory");
 }
-__device__ __forceinline__ void tma_store_4d(const CUtensorMap *map, uint32_t src, int c0, int c1, int c2,
-                                             int c3) {
-  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
-               ::"l"(map), "r"(src), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
-               : "memory");
-}
-__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void tma_store_wait_read() {
-  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
-}
-__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
-__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
@@ -185,19 +183,15 @@ template <typename VolT>
 struct Stg;
 template <>
 struct Stg<__nv_bfloat16> {
-  static constexpr int ES = 2;
   static constexpr int TW = 8;            // tile width, elements
   static constexpr int L0_TILES = 4;      // level-0 tiles per block row of tiles
-  static constexpr int ROWS_PER_STEP = 4;
   static constexpr int L1_UNITS = 8, L2_UNITS = 2;      // 16-byte units per query
   static constexpr int NU = 11;           // L1 (8) + L2 (2) + L3 (1) units per query
 };
 template <>
 struct Stg<float> {
-  static constexpr int ES = 4;
   static constexpr int TW = 4;
   static constexpr int L0_TILES = 8;
-  static constexpr int ROWS_PER_STEP = 2;
   static constexpr int L1_UNITS = 16, L2_UNITS = 4;
   static constexpr int NU = 21;
 };
@@ -225,18 +219,45 @@ __device__ __forceinline__ void put_unit(uint32_t addr, const float *v) {
   else
     sts16(addr, __float_as_uint(v[0]), __float_as_uint(v[1]), __float_as_uint(v[2]), __float_as_uint(v[3]));
 }
-// step buffer: query row of 256 bytes, unit index XOR-rotated by the query so that
-// both the query-major writes and the unit-major read-back are conflict-free
-__device__ __forceinline__ uint32_t step_addr(uint32_t buf, int q, int unit) {
-  return buf + q * 256 + ((unit ^ (q & 7)) << 4);
-}
+// Step buffer: one 256-byte row per query, unit position XOR-rotated by the query
+// (unit u of query q sits at q*256 + ((u ^ (q & 7)) << 4)), so that both the
+// query-major writes and the unit-major read-back are conflict-free.  With a
+// 256-byte-aligned buffer the XOR folds into the address: (row | rot) ^ (u << 4).
 
 // ---------------------------------------------------------------- the kernel
-template <typename VolT>
+// Read one level-0 step (256 bytes per query, 32 queries) back from the step buffer
+// and store it: per instruction, 16 lanes cover the 256 bytes of one query.
+//   ld_base : this lane's read address for iteration 0 (see the rotation above)
+//   g       : this lane's global address for iteration 0; advances 2 queries per iteration
+template <bool FULL>
+__device__ __forceinline__ void flush_step(uint32_t ld_base, char *g, long long stride2, int hi, int nq,
+                                           bool lane_ok) {
+#pragma unroll 8
+  for (int it = 0; it < 16; ++it) {
+    const uint4 val = lds16((ld_base ^ (((2 * it) & 7) << 4)) + it * 512);
+    if (FULL || (lane_ok && 2 * it + hi < nq)) *reinterpret_cast<uint4 *>(g) = val;
+    g += stride2;
+  }
+}
+// Same for a pooled level out of the per-tile buffer: UNITS 16-byte units per query.
+template <int UNITS, bool FULL>
+__device__ __forceinline__ void flush_pooled(uint32_t ld_base, int nu_bytes, char *g, long long stride_q, int sub,
+                                             int nq, bool lane_ok) {
+  constexpr int QPI = 32 / UNITS;       // queries per instruction
+#pragma unroll
+  for (int it = 0; it < 32 / QPI; ++it) {
+    const uint4 val = lds16(ld_base + it * QPI * nu_bytes);
+    if (FULL || (lane_ok && it * QPI + sub < nq)) *reinterpret_cast<uint4 *>(g) = val;
+    g += QPI * stride_q;
+  }
+}
+
+template <typename VolT, bool SCALE>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                         const TcParams p) {
   using S = Stg<VolT>;
+  constexpr int ES = (int)sizeof(VolT);
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // carve (operand offsets are multiples of 1024)
   uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -281,12 +302,10 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
     if (lane == 0) {
       TileWalk walk;
       walk.init();
-      long long cur_key = -1, gt;
+      int b, m, n, by, bx, cur_key = -1;
       uint32_t a_loads = 0, bs = 0;
-      while (walk.next(p, gt)) {
-        const long long key = gt / p.NT;          // (b, m)
-        const int n = (int)(gt - key * p.NT);
-        const int b = (int)(key / p.MT), m = (int)(key - (long long)b * p.MT);
+      while (walk.next(p, b, m, n, by, bx)) {
+        const int key = b * p.MT + m;
         if (key != cur_key) {
           if (a_loads > 0) mbar_wait(bar_a_empty, (a_loads - 1) & 1);
           mbar_expect_tx(bar_a_full, p.KB * A_KB_BYTES);
@@ -308,17 +327,17 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
     if (lane == 0) {
       TileWalk walk;
       walk.init();
-      long long cur_key = -1, gt;
-      bool have = walk.next(p, gt);
+      int b, m, n, by, bx, cur_key = -1;
       uint32_t a_uses = 0, bs = 0, i = 0;
-      while (have) {
-        const long long key = gt / p.NT;
+      while (walk.next(p, b, m, n, by, bx)) {
+        const int key = b * p.MT + m;
         if (key != cur_key) {
           mbar_wait(bar_a_full, a_uses & 1);
           ++a_uses;
           cur_key = key;
         }
         const uint32_t acc = i & 1, use = i >> 1;
+        ++i;
         mbar_wait(bar_t_empty + 8 * acc, (use & 1) ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BN;
@@ -335,11 +354,7 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
           umma_commit(bar_b_empty + 8 * st);   // frees the B stage when these MMAs retire
         }
         umma_commit(bar_t_full + 8 * acc);     // accumulator ready
-        long long gnext;
-        have = walk.next(p, gnext);
-        if (!have || gnext / p.NT != key) umma_commit(bar_a_empty);   // last use of this A operand
-        gt = gnext;
-        ++i;
+        if (walk.a_changes(b, m)) umma_commit(bar_a_empty);   // last use of this A operand
       }
     }
   } else {
@@ -348,29 +363,48 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
     const uint32_t sbuf = sStage + (warp - EPI_WARP0) * stage_bytes_per_warp<VolT>();   // level-0 step buffer
     const uint32_t pbuf = sbuf + STEP_BYTES;                                            // levels 1..3
     const int L = p.num_levels;
+    // per-lane constants of the staging buffers
+    const uint32_t st_base = (sbuf + lane * 256) | ((lane & 7) << 4);    // write: unit u at st_base ^ (u << 4)
+    const uint32_t pb_base = pbuf + lane * (S::NU * 16);                 // write: pooled unit u at pb_base + 16 u
+    const int u16 = lane & 15, hi = lane >> 4;                           // read-back of a step: unit, query parity
+    const uint32_t ld_base = (sbuf + hi * 256) | ((u16 ^ hi) << 4);
+    const int l0_tile = ES == 2 ? (u16 >> 2) : (u16 >> 1);               // tile (inside the chunk) of unit u16
+    constexpr int U1 = S::L1_UNITS, U2 = S::L2_UNITS;
+    const int u1 = lane % U1, sub1 = lane / U1, u2 = lane % U2, sub2 = lane / U2;
+    const uint32_t ld1 = pbuf + (sub1 * S::NU + u1) * 16;
+    const int l2_tile = ES == 2 ? 0 : (u2 >> 1), l2_row = ES == 2 ? u2 : (u2 & 1);
+    const uint32_t ld2 = pbuf + (sub2 * S::NU + U1 + (ES == 2 ? u2 : l2_row + 2 * l2_tile)) * 16;
+
     TileWalk walk;
     walk.init();
-    long long gt;
+    int b, m, n, by, bx;
     uint32_t i = 0;
-    while (walk.next(p, gt)) {
-      const long long key = gt / p.NT;
-      const int n = (int)(gt - key * p.NT);
-      const int b = (int)(key / p.MT), m = (int)(key - (long long)b * p.MT);
-      const int by = n / p.nbx, bx = n - by * p.nbx;   // block coordinates (8 rows x 32 columns)
+    while (walk.next(p, b, m, n, by, bx)) {
       const int x0 = bx * TB_W, y0 = by * TB_H;
       const int qw = m * BM + quarter * 32;            // first query of this warp
       const uint32_t acc = i & 1, use = i >> 1;
       ++i;
-      mbar_wait(bar_t_full + 8 * acc, use & 1);
-      tc_fence_after();
-      const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(quarter * 32) << 16);
-      const long long slab_q0 = (long long)b * p.N + qw;   // slab index of this warp's first query
+      const long long slab_q0 = (long long)b * p.N + qw;    // slab index of this warp's first query
       const int nq = min(32, p.N - qw);                     // valid queries of this warp (may be <= 0)
 
       // valid pooled cells of this block (floor rule of avg_pool2d; the rest is padding -> 0)
       const int nvx1 = p.Wl[1] - (x0 >> 1), nvy1 = p.Hl[1] - (y0 >> 1);
       const int nvx2 = p.Wl[2] - (x0 >> 2), nvy2 = p.Hl[2] - (y0 >> 2);
       const int nvx3 = p.Wl[3] - (x0 >> 3), nvy3 = p.Hl[3] - (y0 >> 3);
+      const bool edge = (L > 1 && (nvx1 < 16 || nvy1 < 4)) || (L > 2 && (nvx2 < 8 || nvy2 < 2)) ||
+                        (L > 3 && (nvx3 < 4 || nvy3 < 1));
+      // level-0 chunk of this block: tiles tx0 .. tx0 + L0_TILES - 1 of tile rows (y0 >> 2), (y0 >> 2) + 1
+      const int tx0 = x0 / S::TW;
+      const int nt0 = min(S::L0_TILES, p.tiles_x[0] - tx0);
+      const bool full0 = nq == 32 && nt0 == S::L0_TILES;
+      const long long slab0B = p.slab[0] * ES;
+      char *g0 = (char *)p.lvl[0] + ((long long)(y0 >> 2) * p.tiles_x[0] + tx0) * 64 + (slab_q0 + hi) * slab0B +
+                 (ES == 2 ? u16 * 16 : (u16 >> 1) * 64 + (u16 & 1) * 16);
+      const long long tile_row0B = (long long)p.tiles_x[0] * 64;
+
+      mbar_wait(bar_t_full + 8 * acc, use & 1);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(quarter * 32) << 16);
 
       float p1prev[16], p2prev[8];
 #pragma unroll
@@ -388,58 +422,58 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
         float v0[32], v1[32], p1[16];
 #pragma unroll
         for (int k = 0; k < 32; ++k) {
-          v0[k] = __uint_as_float(r0[k]) * p.scale;
-          v1[k] = __uint_as_float(r1[k]) * p.scale;
+          v0[k] = __uint_as_float(r0[k]);
+          v1[k] = __uint_as_float(r1[k]);
+          if (SCALE) { v0[k] *= p.scale; v1[k] *= p.scale; }
         }
         // ---- level 0 units of block rows 2rp, 2rp+1
-        if (sizeof(VolT) == 2) {
+        if (ES == 2) {
           const int r = (2 * rp) & 3;                    // row inside the tile
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
-            put_unit<VolT>(step_addr(sbuf, lane, k * 4 + r), v0 + 8 * k);
-            put_unit<VolT>(step_addr(sbuf, lane, k * 4 + r + 1), v1 + 8 * k);
+            put_unit<VolT>(st_base ^ ((k * 4 + r) << 4), v0 + 8 * k);
+            put_unit<VolT>(st_base ^ ((k * 4 + r + 1) << 4), v1 + 8 * k);
           }
         } else {
 #pragma unroll
           for (int k = 0; k < 8; ++k) {
-            put_unit<VolT>(step_addr(sbuf, lane, k * 2), v0 + 4 * k);
-            put_unit<VolT>(step_addr(sbuf, lane, k * 2 + 1), v1 + 4 * k);
+            put_unit<VolT>(st_base ^ ((k * 2) << 4), v0 + 4 * k);
+            put_unit<VolT>(st_base ^ ((k * 2 + 1) << 4), v1 + 4 * k);
           }
         }
         // ---- pooled levels, from the fp32 values
 #pragma unroll
-        for (int k = 0; k < 16; ++k) {
-          const float a = 0.25f * ((v0[2 * k] + v0[2 * k + 1]) + (v1[2 * k] + v1[2 * k + 1]));
-          p1[k] = (k < nvx1 && rp < nvy1) ? a : 0.f;
+        for (int k = 0; k < 16; ++k) p1[k] = 0.25f * ((v0[2 * k] + v0[2 * k + 1]) + (v1[2 * k] + v1[2 * k + 1]));
+        if (edge) {
+#pragma unroll
+          for (int k = 0; k < 16; ++k) p1[k] = (k < nvx1 && rp < nvy1) ? p1[k] : 0.f;
         }
         if (L > 1) {
 #pragma unroll
-          for (int k = 0; k < 16 / S::TW; ++k) put_unit<VolT>(pbuf + (lane * S::NU + k * 4 + rp) * 16, p1 + S::TW * k);
+          for (int k = 0; k < 16 / S::TW; ++k) put_unit<VolT>(pb_base + (k * 4 + rp) * 16, p1 + S::TW * k);
         }
         if (rp & 1) {
           float p2[8];
 #pragma unroll
-          for (int k = 0; k < 8; ++k) {
-            const float a = 0.25f * ((p1prev[2 * k] + p1prev[2 * k + 1]) + (p1[2 * k] + p1[2 * k + 1]));
-            p2[k] = (k < nvx2 && (rp >> 1) < nvy2) ? a : 0.f;
+          for (int k = 0; k < 8; ++k)
+            p2[k] = 0.25f * ((p1prev[2 * k] + p1prev[2 * k + 1]) + (p1[2 * k] + p1[2 * k + 1]));
+          if (edge) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) p2[k] = (k < nvx2 && (rp >> 1) < nvy2) ? p2[k] : 0.f;
           }
           if (L > 2) {
-            if (sizeof(VolT) == 2) {
-              put_unit<VolT>(pbuf + (lane * S::NU + S::L1_UNITS + (rp >> 1)) * 16, p2);
-            } else {
-              put_unit<VolT>(pbuf + (lane * S::NU + S::L1_UNITS + (rp >> 1)) * 16, p2);
-              put_unit<VolT>(pbuf + (lane * S::NU + S::L1_UNITS + 2 + (rp >> 1)) * 16, p2 + 4);
-            }
+            put_unit<VolT>(pb_base + (U1 + (rp >> 1)) * 16, p2);
+            if (ES == 4) put_unit<VolT>(pb_base + (U1 + 2 + (rp >> 1)) * 16, p2 + 4);
           }
           if (rp == 3) {
             float p3[8];
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
               const float a = 0.25f * ((p2prev[2 * k] + p2prev[2 * k + 1]) + (p2[2 * k] + p2[2 * k + 1]));
-              p3[k] = (k < nvx3 && 0 < nvy3) ? a : 0.f;
+              p3[k] = (!edge || (k < nvx3 && 0 < nvy3)) ? a : 0.f;
               p3[4 + k] = 0.f;
             }
-            if (L > 3) put_unit<VolT>(pbuf + (lane * S::NU + S::L1_UNITS + S::L2_UNITS) * 16, p3);
+            if (L > 3) put_unit<VolT>(pb_base + (U1 + U2) * 16, p3);
           } else {
 #pragma unroll
             for (int k = 0; k < 8; ++k) p2prev[k] = p2[k];
@@ -450,26 +484,15 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
         }
 
         // ---- a level-0 step is complete: read it back query by query, coalesced stores
-        if (sizeof(VolT) == 4 || (rp & 1)) {
+        if (ES == 4 || (rp & 1)) {
           __syncwarp();
-          const int step = sizeof(VolT) == 2 ? (rp >> 1) : rp;
-          // tile row this step lands in, and the byte offset inside the tiles
-          const int ty = (y0 >> 2) + (sizeof(VolT) == 2 ? step : (step >> 1));
-          const int tx0 = x0 / S::TW;
-          const int nt = min(S::L0_TILES, p.tiles_x[0] - tx0);      // tiles of the chunk that exist
-          if (ty < p.tiles_y[0] && nt > 0) {
-            VolT *base = (VolT *)p.lvl[0] + ((long long)ty * p.tiles_x[0] + tx0) * (TILE_H * S::TW);
-            const int u = lane & 15;
-            // unit u of a query's step -> byte offset inside the chunk, and its tile
-            const int tile = sizeof(VolT) == 2 ? (u >> 2) : (u >> 1);
-            const int off = sizeof(VolT) == 2 ? u * 16 : (u >> 1) * 64 + (step & 1) * 32 + (u & 1) * 16;
-#pragma unroll 4
-            for (int it = 0; it < 16; ++it) {
-              const int ql = 2 * it + (lane >> 4);
-              const uint4 val = lds16(step_addr(sbuf, ql, u));
-              if (ql < nq && tile < nt)
-                *reinterpret_cast<uint4 *>((char *)(base + (slab_q0 + ql) * p.slab[0]) + off) = val;
-            }
+          // bf16: step = one row of tiles; fp32: step = two of the four rows of a row of tiles
+          const int trow = ES == 2 ? (rp >> 1) : (rp >> 1);
+          const int half = ES == 2 ? 0 : (rp & 1) * 32;
+          if ((y0 >> 2) + trow < p.tiles_y[0] && nt0 > 0) {
+            char *g = g0 + trow * tile_row0B + half;
+            if (full0) flush_step<true>(ld_base, g, 2 * slab0B, hi, nq, true);
+            else flush_step<false>(ld_base, g, 2 * slab0B, hi, nq, l0_tile < nt0);
           }
           __syncwarp();
         }
@@ -478,54 +501,38 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
       // ---- levels 1..3 of this block
       __syncwarp();
       if (L > 1) {
-        constexpr int U1 = S::L1_UNITS, QPI = 32 / U1;       // units and queries per instruction
-        const int ty = y0 >> 3, tx0 = (x0 >> 1) / S::TW;
-        const int nt = min(U1 / 4, p.tiles_x[1] - tx0);
+        const int ty = y0 >> 3, tx1 = (x0 >> 1) / S::TW;
+        const int nt = min(U1 / 4, p.tiles_x[1] - tx1);
         if (ty < p.tiles_y[1] && nt > 0) {
-          VolT *base = (VolT *)p.lvl[1] + ((long long)ty * p.tiles_x[1] + tx0) * (TILE_H * S::TW);
-          const int u = lane % U1;
-#pragma unroll 4
-          for (int it = 0; it < 32 / QPI; ++it) {
-            const int ql = it * QPI + lane / U1;
-            const uint4 val = lds16(pbuf + (ql * S::NU + u) * 16);
-            if (ql < nq && (u >> 2) < nt)
-              *reinterpret_cast<uint4 *>((char *)(base + (slab_q0 + ql) * p.slab[1]) + u * 16) = val;
-          }
+          const long long slabB = p.slab[1] * ES;
+          char *g = (char *)p.lvl[1] + ((long long)ty * p.tiles_x[1] + tx1) * 64 + (slab_q0 + sub1) * slabB + u1 * 16;
+          if (nq == 32 && nt == U1 / 4) flush_pooled<U1, true>(ld1, S::NU * 16, g, slabB, sub1, nq, true);
+          else flush_pooled<U1, false>(ld1, S::NU * 16, g, slabB, sub1, nq, (u1 >> 2) < nt);
         }
       }
       if (L > 2) {
-        constexpr int U2 = S::L2_UNITS, QPI = 32 / U2;
-        const int ty = y0 >> 4, tx0 = (x0 >> 2) / S::TW;
+        const int ty = y0 >> 4, tx2 = (x0 >> 2) / S::TW;
         const int row0 = (y0 >> 2) & 3;                       // first of the block's two rows inside the tile
         if (ty < p.tiles_y[2]) {
-          VolT *base = (VolT *)p.lvl[2] + ((long long)ty * p.tiles_x[2] + tx0) * (TILE_H * S::TW);
-          const int u = lane % U2;
-          // bf16: units = rows 0,1 of one tile;  fp32: unit = tile * 2 + row ... stored as [row + 2*tile]
-          const int tile = sizeof(VolT) == 2 ? 0 : (u >> 1);
-          const int row = sizeof(VolT) == 2 ? u : (u & 1);
-          const int off = tile * 64 + (row0 + row) * 16;
-#pragma unroll
-          for (int it = 0; it < 32 / QPI; ++it) {
-            const int ql = it * QPI + lane / U2;
-            const uint4 val = lds16(pbuf + (ql * S::NU + S::L1_UNITS + (sizeof(VolT) == 2 ? u : row + 2 * tile)) * 16);
-            if (ql < nq && tx0 + tile < p.tiles_x[2])
-              *reinterpret_cast<uint4 *>((char *)(base + (slab_q0 + ql) * p.slab[2]) + off) = val;
-          }
+          const long long slabB = p.slab[2] * ES;
+          char *g = (char *)p.lvl[2] + ((long long)ty * p.tiles_x[2] + tx2) * 64 + (slab_q0 + sub2) * slabB +
+                    l2_tile * 64 + (row0 + l2_row) * 16;
+          flush_pooled<U2, false>(ld2, S::NU * 16, g, slabB, sub2, nq, tx2 + l2_tile < p.tiles_x[2]);
         }
       }
       if (L > 3) {
         const int ty = y0 >> 5, tx = (x0 >> 3) / S::TW;
         const int row = (y0 >> 3) & 3;
         if (ty < p.tiles_y[3] && tx < p.tiles_x[3] && lane < nq) {
-          char *dst = (char *)((VolT *)p.lvl[3] + ((long long)ty * p.tiles_x[3] + tx) * (TILE_H * S::TW) +
-                               (slab_q0 + lane) * p.slab[3]) + row * 16;
-          const uint4 val = lds16(pbuf + (lane * S::NU + S::L1_UNITS + S::L2_UNITS) * 16);
-          if (sizeof(VolT) == 4) {
+          char *dst = (char *)p.lvl[3] + ((long long)ty * p.tiles_x[3] + tx) * 64 + (slab_q0 + lane) * p.slab[3] * ES +
+                      row * 16;
+          const uint4 val = lds16(pb_base + (U1 + U2) * 16);
+          if (ES == 4) {
             *reinterpret_cast<uint4 *>(dst) = val;
           } else {
             // 4 cells = 8 bytes: the left or right half of a tile row.  The left writer also
             // zeroes the right half when no block to its right exists (padding columns).
-            const bool right = ((x0 >> 3) & 7) != 0;
+            const bool right = (bx & 1) != 0;
             if (right) *reinterpret_cast<uint2 *>(dst + 8) = make_uint2(val.x, val.y);
             else if (bx + 1 < p.nbx) *reinterpret_cast<uint2 *>(dst) = make_uint2(val.x, val.y);
             else *reinterpret_cast<uint4 *>(dst) = val;
@@ -601,7 +608,8 @@ int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, con
   p.NT = p.nbx * ceil_div(H, TB_H);
   p.KB = ceil_div(D, BK);
   p.num_levels = L;
-  p.scale = 1.0f / sqrtf((float)D);
+  float pre_scale = 1.f;
+  split_scale(D, &pre_scale, &p.scale);      // pre_scale was applied to fmap1 by the pack
   for (int l = 0; l < 4; ++l) {
     const bool on = l < L;
     p.Hl[l] = on ? lay.H[l] : 0;
@@ -654,7 +662,7 @@ int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, con
     if (r) return r;
   }
 
-  auto kern = build_pyramid_tc_kernel<VolT>;
+  auto kern = p.scale == 1.f ? build_pyramid_tc_kernel<VolT, false> : build_pyramid_tc_kernel<VolT, true>;
   RC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const long long group_tiles = (long long)p.group_pairs * tpp;
   const int grid = group_tiles < sms ? (int)group_tiles : sms;

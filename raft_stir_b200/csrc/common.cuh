@@ -4,6 +4,7 @@
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <math.h>
 #include <stdio.h>
 
 #include "../../include/raft_corr.h"
@@ -43,6 +44,22 @@ void set_error(const char *fmt, ...);   // api.cu; thread-local message
 // ---- small helpers ---------------------------------------------------------
 __host__ __device__ inline int64_t round_up64(int64_t v, int64_t m) { return (v + m - 1) / m * m; }
 __host__ __device__ inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+
+// 1/sqrt(D) = pre * post with pre an exact power of two (applied to fmap1 by the
+// pack: scaling bf16 by a power of two commutes with rounding) and post the rest,
+// applied to the fp32 accumulators.  For D a power of 4 (RAFT-basic's 256) post
+// is exactly 1 and the build's epilogue skips the multiply.
+inline void split_scale(int D, float *pre, float *post) {
+  int k = 0;
+  while ((1 << (2 * (k + 1))) <= D) ++k;          // 4^k <= D
+  if ((1 << (2 * k)) == D) {
+    *pre = 1.0f / (float)(1 << k);
+    *post = 1.0f;
+  } else {
+    *pre = 1.0f;
+    *post = 1.0f / sqrtf((float)D);
+  }
+}
 
 // Device-side copy of the layout: passed by value to kernels.
 struct Levels {

@@ -6,7 +6,8 @@
 // fp32 for kind::tf32), and wants fmap2's pixels ordered by 8x32 spatial block
 // so that a 256-column GEMM tile is one block (common.cuh: TB_H, TB_W).
 //
-//   f1p[b][q][d]                      q = y*W + x                 (N rows)
+//   f1p[b][q][d]                      q = y*W + x                 (N rows), times the
+//                                          exact power-of-two part of 1/sqrt(D)
 //   f2p[b][blk*256 + (y%8)*32 + x%32][d]   blk = (y/8)*nbx + x/32   (nblk*256 rows,
 //                                          rows outside the map are zero)
 //
@@ -36,7 +37,7 @@ template <typename OutT>
 __global__ void __launch_bounds__(256)
 pack_features_kernel(const float *__restrict__ fmap1, const float *__restrict__ fmap2,
                      OutT *__restrict__ f1p, OutT *__restrict__ f2p, int D, int H, int W,
-                     int groups1, int nbx, long long rows2) {
+                     int groups1, int nbx, long long rows2, float scale1) {
   __shared__ float tile[PK_D][PK_ROWS + 1];
   const int N = H * W;
   const int b = blockIdx.z;
@@ -61,11 +62,12 @@ pack_features_kernel(const float *__restrict__ fmap1, const float *__restrict__ 
     if (y < H && x < W) src = y * W + x;
   }
   const float *in = (second ? fmap2 : fmap1) + (size_t)b * D * N;
+  const float mul = second ? 1.f : scale1;     // exact power of two (common.cuh: split_scale)
 #pragma unroll
   for (int k = 0; k < PK_D / 8; ++k) {
     int d = wid + 8 * k;
     float v = 0.f;
-    if (src >= 0 && d0 + d < D) v = __ldg(in + (size_t)(d0 + d) * N + src);
+    if (src >= 0 && d0 + d < D) v = mul * __ldg(in + (size_t)(d0 + d) * N + src);
     tile[d][lane] = v;
   }
   __syncthreads();
@@ -90,12 +92,14 @@ int launch_pack(const float *fmap1, const float *fmap2, int B, int D, int H, int
   const int groups1 = ceil_div(N, PK_ROWS);
   const int groups2 = (int)(rows2 / PK_ROWS);
   dim3 grid(groups1 + groups2, ceil_div(D, PK_D), B);
+  float pre = 1.f, post = 1.f;
+  split_scale(D, &pre, &post);
   if (math == RC_MATH_BF16) {
     pack_features_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>(
-        fmap1, fmap2, (__nv_bfloat16 *)f1p, (__nv_bfloat16 *)f2p, D, H, W, groups1, nbx, rows2);
+        fmap1, fmap2, (__nv_bfloat16 *)f1p, (__nv_bfloat16 *)f2p, D, H, W, groups1, nbx, rows2, pre);
   } else {
     pack_features_kernel<float><<<grid, 256, 0, s>>>(fmap1, fmap2, (float *)f1p, (float *)f2p, D, H,
-                                                     W, groups1, nbx, rows2);
+                                                     W, groups1, nbx, rows2, pre);
   }
   RC_LAUNCH_CHECK("pack_features_kernel");
   return RC_OK;
