@@ -8,21 +8,24 @@
 //
 // as a tcgen05 GEMM (kind::f16, bf16 operands, fp32 accumulators in TMEM),
 // 128 queries x 256 targets per tile, operands staged by TMA with the 128-byte
-// swizzle.  A 256-target tile is one 8x32 spatial block of fmap2 (pack.cu), so a
-// thread of the epilogue, which owns one query row of the accumulator, holds
-// complete 2x2 / 4x4 / 8x8 pooling footprints in registers: levels 1..3 are
-// in-register sums of the fp32 accumulators (no re-read of level 0, no extra
-// rounding), written together with level 0.
+// swizzle.  A 256-target tile is one 8x32 spatial block of fmap2 (pack.cu), so
+// complete 2x2 / 4x4 / 8x8 pooling footprints sit in one accumulator row:
+// levels 1..3 are in-register sums of the fp32 accumulators (no re-read of
+// level 0, no extra rounding), written together with level 0, all in the
+// 64-byte-tile layout of rc_layout.
 //
-// Warp roles (192 threads, 1 CTA per SM, persistent over a contiguous range of
-// tiles):  warp 0 = TMA producer, warp 1 = MMA issuer + TMEM owner,
-// warps 2..5 = epilogue (TMEM lane quarter = warp % 4).
+// Warp roles (320 threads, 1 CTA per SM, persistent):  warp 0 = TMA producer,
+// warp 1 = MMA issuer + TMEM owner, warps 2..9 = epilogue in two groups of four
+// (TMEM lane quarter = warp % 4).  Group g takes block columns 16g..16g+15 of
+// all 8 rows of every tile: a complete 8x16 sub-block, so all pooled levels stay
+// thread-local.  An epilogue warp copies its 128 accumulator values to
+// registers with eight tcgen05.ld and hands the accumulator back at once; the
+// conversion, pooling and stores then overlap the MMAs of the next tiles.
 // Pipelines: A (the 128-query operand) is stationary in smem for all tiles of
-// one query block; B k-blocks stream through a ring; two 256-column TMEM
-// accumulators let the epilogue of tile i overlap the MMAs of tile i+1.
-// Epilogue output goes through swizzled smem staging and TMA tensor stores
-// against 4-D maps (x, y, q, b) of each level, whose true extents (W>>l, H>>l,
-// N) clip edge tiles -- which is exactly avg_pool2d's floor rule.
+// one query block; B k-blocks (32 KB) stream through a ring; two 256-column
+// TMEM accumulators alternate.  The single-thread producer and MMA loops keep
+// stage index and phase incrementally (no divisions): their per-stage overhead
+// is on the critical path of the tensor pipe.
 #include <cuda.h>
 
 #include "common.cuh"
@@ -36,8 +39,11 @@ constexpr int BK = 64;           // bf16 elements per k-block (128 bytes = swizz
 constexpr int UMMA_K = 16;
 constexpr int A_KB_BYTES = BM * 128;   // 16 KB
 constexpr int B_ST_BYTES = BN * 128;   // 32 KB
-constexpr int TC_THREADS = 192;
+constexpr int MAX_STAGES = 4;
 constexpr int EPI_WARP0 = 2;
+constexpr int EPI_WARPS = 8;           // two groups of four
+constexpr int TC_THREADS = 32 * (EPI_WARP0 + EPI_WARPS);
+constexpr int GW = TB_W / 2;           // block columns per epilogue group (16)
 
 struct TcParams {
   int B, N, MT, NT, nbx, KB, num_levels, stages;
@@ -54,8 +60,7 @@ struct TcParams {
 // contiguous range of the group's tiles in (b, m, n) order (balanced to within
 // one tile; a range stays on one query block for NT tiles, so the A operand is
 // reloaded rarely).  Grouping keeps the packed fmap2 of only a few pairs hot in
-// L2 next to the output stream; one range over all pairs has every pair's
-// operand in flight at once and misses.  Divisions happen once per range.
+// L2 next to the output stream.  Divisions happen once per range.
 struct TileWalk {
   int grp, left;              // current group, tiles left in this CTA's range of it
   int b, m, n, by, bx;        // the next tile; (by, bx) = n's block coordinates
@@ -104,20 +109,24 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
-// Bounded wait: a protocol bug must surface as a launch error, never as a hung GPU.
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  uint32_t ok = 0;
+__device__ __forceinline__ bool mbar_try(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+// Slow path of a wait, bounded: a protocol bug must surface as a launch error,
+// never as a hung GPU.
+__device__ __noinline__ void mbar_wait_slow(uint32_t bar, uint32_t parity) {
   unsigned long long t0 = 0;
-  for (uint32_t spin = 0;; ++spin) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(ok)
-        : "r"(bar), "r"(parity)
-        : "memory");
-    if (ok) return;
-    if ((spin & 0x3ff) == 0x3ff) {
+  for (uint32_t spin = 1;; ++spin) {
+    if (mbar_try(bar, parity)) return;
+    if ((spin & 0xff) == 0) {
       unsigned long long now;
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
       if (t0 == 0) t0 = now;
@@ -125,13 +134,39 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     }
   }
 }
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  if (!mbar_try(bar, parity)) mbar_wait_slow(bar, parity);
+}
+// L2 eviction policies: the packed operands are re-read by every CTA (keep them),
+// the volume is written once and not read by this kernel (let it go first).
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
 __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0,
-                                            int c1, int c2) {
+                                            int c1, int c2, uint64_t policy) {
   asm volatile(
-      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes"
-      " [%0], [%1, {%3, %4, %5}], [%2];"
-      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
+      " [%0], [%1, {%3, %4, %5}], [%2], %6;"
+      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "l"(policy)
       : "memory");
+}
+__device__ __forceinline__ void stg16_hint(void *dst, const uint4 &v, uint64_t policy) {
+  asm volatile("st.global.L2::cache_hint.v4.b32 [%0], {%1, %2, %3, %4}, %5;" ::"l"(dst), "r"(v.x), "r"(v.y), "r"(v.z),
+               "r"(v.w), "l"(policy)
+               : "memory");
+}
+__device__ __forceinline__ void stg8_hint(void *dst, uint32_t a, uint32_t b, uint64_t policy) {
+  asm volatile("st.global.L2::cache_hint.v2.b32 [%0], {%1, %2}, %3;" ::"l"(dst), "r"(a), "r"(b), "l"(policy) : "memory");
+}
+__device__ __forceinline__ void stg4_hint(void *dst, uint32_t a, uint64_t policy) {
+  asm volatile("st.global.L2::cache_hint.b32 [%0], %1, %2;" ::"l"(dst), "r"(a), "l"(policy) : "memory");
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -147,57 +182,54 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint6
       ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+// 32 TMEM lanes x 16 consecutive columns -> 16 registers per thread (lane = this thread's query)
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t *r) {
   asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
       : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
-        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
-        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
       : "r"(taddr));
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // K-major, 128-byte-swizzled operand tile: rows of 128 bytes, 8-row groups 1024 bytes apart.
-__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
-  const uint32_t lo = ((saddr >> 4) & 0x3fffu) | (1u << 16);            // start address, LBO = 1 (unused)
-  const uint32_t hi = (1024u >> 4) | (1u << 14) | (2u << 29);           // SBO, version 1, SWIZZLE_128B
-  return ((uint64_t)hi << 32) | lo;
-}
+// hi word: SBO = 1024 B, version 1, SWIZZLE_128B;  lo word: start address >> 4, LBO = 1 (unused).
+constexpr uint32_t DESC_HI = (1024u >> 4) | (1u << 14) | (2u << 29);
+__device__ __forceinline__ uint32_t desc_lo(uint32_t saddr) { return ((saddr >> 4) & 0x3fffu) | (1u << 16); }
+__device__ __forceinline__ uint64_t desc_make(uint32_t lo) { return ((uint64_t)DESC_HI << 32) | lo; }
 // kind::f16: D = F32 (bit 4), A = B = BF16 (bits 7, 10), both K-major, N>>3 at 17, M>>4 at 24
 constexpr uint32_t IDESC_BF16 = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) |
                                 ((uint32_t)(BM >> 4) << 24);
 
 // ---------------------------------------------------------------- epilogue staging
-// An epilogue thread owns one query (TMEM lane) and sees the 8x32 target block
-// two rows at a time.  Level 0 is written in STEPS of 256 bytes per query (bf16:
-// 4 block rows = one row of 4 tiles, contiguous; fp32: 2 block rows = half of a
-// row of 8 tiles, 8 pieces of 32 bytes): the thread parks its 16-byte units in a
-// per-warp buffer, then the warp reads the buffer back query by query and issues
-// coalesced 16-byte stores (a full 256-byte chunk per half warp).  Levels 1..3
-// of the block (168 / 336 bytes per query) collect in a second buffer and leave
-// once per tile the same way.
+// An epilogue thread owns one query (TMEM lane) and an 8 x 16 sub-block of the
+// tile's targets.  Level 0 leaves in STEPS of 128 bytes per query (bf16: 4 block
+// rows = 2 tiles, contiguous; fp32: 2 block rows = half of 4 tiles, 4 pieces of
+// 32 bytes): the thread parks its 16-byte units in a per-warp buffer, then the
+// warp reads the buffer back query by query and issues coalesced 16-byte stores
+// (8 lanes cover one query's 128 bytes).  The level-1 cells of the sub-block
+// (64 / 128 bytes per query) take the same route once per tile.  Levels 2 and 3
+// (20 / 40 bytes per query and tile) are stored by the owning thread directly.
 template <typename VolT>
 struct Stg;
 template <>
 struct Stg<__nv_bfloat16> {
   static constexpr int TW = 8;            // tile width, elements
-  static constexpr int L0_TILES = 4;      // level-0 tiles per block row of tiles
-  static constexpr int L1_UNITS = 8, L2_UNITS = 2;      // 16-byte units per query
-  static constexpr int NU = 11;           // L1 (8) + L2 (2) + L3 (1) units per query
+  static constexpr int L0_GT = 2;         // level-0 tiles per group and row of tiles
+  static constexpr int L1_GT = 1;         // level-1 tiles per group
+  static constexpr int STEPS = 2;         // level-0 steps per tile
 };
 template <>
 struct Stg<float> {
   static constexpr int TW = 4;
-  static constexpr int L0_TILES = 8;
-  static constexpr int L1_UNITS = 16, L2_UNITS = 4;
-  static constexpr int NU = 21;
+  static constexpr int L0_GT = 4;
+  static constexpr int L1_GT = 2;
+  static constexpr int STEPS = 4;
 };
-constexpr int STEP_BYTES = 32 * 256;      // per-warp level-0 step buffer
-template <typename VolT>
-constexpr int stage_bytes_per_warp() { return STEP_BYTES + 32 * Stg<VolT>::NU * 16; }
+constexpr int STEP_BYTES = 32 * 128;      // per-warp level-0 step buffer
+constexpr int L1BUF_BYTES = 32 * 128;     // per-warp level-1 buffer (bf16 uses half)
+constexpr int STAGE_BYTES_PER_WARP = STEP_BYTES + L1BUF_BYTES;
 
 __device__ __forceinline__ void sts16(uint32_t addr, uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
@@ -211,7 +243,7 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
   __nv_bfloat162 p = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t *>(&p);
 }
-// 16-byte unit number `n` of a value row (8 bf16 or 4 fp32 elements) -> smem
+// one 16-byte unit (8 bf16 or 4 fp32 values) -> shared memory
 template <typename VolT>
 __device__ __forceinline__ void put_unit(uint32_t addr, const float *v) {
   if (sizeof(VolT) == 2)
@@ -219,39 +251,36 @@ __device__ __forceinline__ void put_unit(uint32_t addr, const float *v) {
   else
     sts16(addr, __float_as_uint(v[0]), __float_as_uint(v[1]), __float_as_uint(v[2]), __float_as_uint(v[3]));
 }
-// Step buffer: one 256-byte row per query, unit position XOR-rotated by the query
-// (unit u of query q sits at q*256 + ((u ^ (q & 7)) << 4)), so that both the
-// query-major writes and the unit-major read-back are conflict-free.  With a
-// 256-byte-aligned buffer the XOR folds into the address: (row | rot) ^ (u << 4).
+// Buffers with 128-byte query rows: unit u of query q sits at q*128 + ((u ^ (q & 7)) << 4),
+// so both the query-major writes and the unit-major read-back are conflict-free.  With a
+// 128-byte-aligned row the XOR folds into the address: (row | rot) ^ (u << 4).
+// Read-back of such a buffer and coalesced store: 8 lanes cover one query's 128 bytes,
+// 4 queries per instruction.
+//   ld_base : this lane's read address for iteration 0;  g : its global address for iteration 0
+template <bool FULL>
+__device__ __forceinline__ void flush128(uint32_t ld_base, char *g, long long stride4, int sub, int nq, bool lane_ok,
+                                         uint64_t pol) {
+#pragma unroll
+  for (int it = 0; it < 8; ++it) {
+    const uint4 val = lds16((ld_base ^ (((4 * it) & 7) << 4)) + it * 512);
+    if (FULL || (lane_ok && 4 * it + sub < nq)) stg16_hint(g, val, pol);
+    g += stride4;
+  }
+}
+// Same for 64-byte query rows (bf16 level 1): unit u of query q at q*64 + ((u ^ ((q >> 1) & 3)) << 4);
+// 4 lanes per query, 8 queries per instruction.
+template <bool FULL>
+__device__ __forceinline__ void flush64(uint32_t ld_base, char *g, long long stride8, int sub, int nq, bool lane_ok,
+                                        uint64_t pol) {
+#pragma unroll
+  for (int it = 0; it < 4; ++it) {
+    const uint4 val = lds16(ld_base + it * 512);
+    if (FULL || (lane_ok && 8 * it + sub < nq)) stg16_hint(g, val, pol);
+    g += stride8;
+  }
+}
 
 // ---------------------------------------------------------------- the kernel
-// Read one level-0 step (256 bytes per query, 32 queries) back from the step buffer
-// and store it: per instruction, 16 lanes cover the 256 bytes of one query.
-//   ld_base : this lane's read address for iteration 0 (see the rotation above)
-//   g       : this lane's global address for iteration 0; advances 2 queries per iteration
-template <bool FULL>
-__device__ __forceinline__ void flush_step(uint32_t ld_base, char *g, long long stride2, int hi, int nq,
-                                           bool lane_ok) {
-#pragma unroll 8
-  for (int it = 0; it < 16; ++it) {
-    const uint4 val = lds16((ld_base ^ (((2 * it) & 7) << 4)) + it * 512);
-    if (FULL || (lane_ok && 2 * it + hi < nq)) *reinterpret_cast<uint4 *>(g) = val;
-    g += stride2;
-  }
-}
-// Same for a pooled level out of the per-tile buffer: UNITS 16-byte units per query.
-template <int UNITS, bool FULL>
-__device__ __forceinline__ void flush_pooled(uint32_t ld_base, int nu_bytes, char *g, long long stride_q, int sub,
-                                             int nq, bool lane_ok) {
-  constexpr int QPI = 32 / UNITS;       // queries per instruction
-#pragma unroll
-  for (int it = 0; it < 32 / QPI; ++it) {
-    const uint4 val = lds16(ld_base + it * QPI * nu_bytes);
-    if (FULL || (lane_ok && it * QPI + sub < nq)) *reinterpret_cast<uint4 *>(g) = val;
-    g += QPI * stride_q;
-  }
-}
-
 template <typename VolT, bool SCALE>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
@@ -264,14 +293,14 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
   const uint32_t sA = smem_u32(smem);
   const uint32_t sB = sA + p.KB * A_KB_BYTES;
   const uint32_t sStage = sB + p.stages * B_ST_BYTES;
-  const uint32_t sBar = sStage + 4 * stage_bytes_per_warp<VolT>();
+  const uint32_t sBar = sStage + EPI_WARPS * STAGE_BYTES_PER_WARP;
   uint32_t *tmem_slot = (uint32_t *)(smem + (sBar - sA) + 128);
   // barrier table (8 bytes each)
   const uint32_t bar_a_full = sBar, bar_a_empty = sBar + 8;
-  const uint32_t bar_b_full = sBar + 16;            // [stages]
-  const uint32_t bar_b_empty = sBar + 16 + 8 * 4;   // [stages] (stages <= 4)
-  const uint32_t bar_t_full = sBar + 16 + 8 * 8;    // [2]
-  const uint32_t bar_t_empty = bar_t_full + 16;     // [2]
+  const uint32_t bar_b_full = sBar + 16;                        // [stages]
+  const uint32_t bar_b_empty = sBar + 16 + 8 * MAX_STAGES;      // [stages]
+  const uint32_t bar_t_full = sBar + 16 + 8 * 2 * MAX_STAGES;   // [2]
+  const uint32_t bar_t_empty = bar_t_full + 16;                 // [2]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -284,7 +313,7 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(bar_t_full + 8 * s, 1);
-      mbar_init(bar_t_empty + 8 * s, 4);
+      mbar_init(bar_t_empty + 8 * s, EPI_WARPS);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -300,25 +329,28 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
   if (warp == 0) {
     // ===================================================== TMA producer
     if (lane == 0) {
+      const uint64_t pol_in = l2_policy_evict_last();
       TileWalk walk;
       walk.init();
       int b, m, n, by, bx, cur_key = -1;
-      uint32_t a_loads = 0, bs = 0;
+      uint32_t a_par = 0;                    // parity of the A-empty phase to wait for next
+      bool a_loaded = false;
+      uint32_t st = 0, ph = 0;               // B ring: stage, parity of its current round
       while (walk.next(p, b, m, n, by, bx)) {
         const int key = b * p.MT + m;
         if (key != cur_key) {
-          if (a_loads > 0) mbar_wait(bar_a_empty, (a_loads - 1) & 1);
+          if (a_loaded) { mbar_wait(bar_a_empty, a_par); a_par ^= 1; }
           mbar_expect_tx(bar_a_full, p.KB * A_KB_BYTES);
           for (int kb = 0; kb < p.KB; ++kb)
-            tma_load_3d(sA + kb * A_KB_BYTES, &map_a, bar_a_full, kb * BK, m * BM, b);
-          ++a_loads;
+            tma_load_3d(sA + kb * A_KB_BYTES, &map_a, bar_a_full, kb * BK, m * BM, b, pol_in);
+          a_loaded = true;
           cur_key = key;
         }
-        for (int kb = 0; kb < p.KB; ++kb, ++bs) {
-          const uint32_t st = bs % p.stages, ph = (bs / p.stages) & 1;
+        for (int kb = 0; kb < p.KB; ++kb) {
           mbar_wait(bar_b_empty + 8 * st, ph ^ 1);
           mbar_expect_tx(bar_b_full + 8 * st, B_ST_BYTES);
-          tma_load_3d(sB + st * B_ST_BYTES, &map_b, bar_b_full + 8 * st, kb * BK, n * BN, b);
+          tma_load_3d(sB + st * B_ST_BYTES, &map_b, bar_b_full + 8 * st, kb * BK, n * BN, b, pol_in);
+          if (++st == (uint32_t)p.stages) { st = 0; ph ^= 1; }
         }
       }
     }
@@ -328,218 +360,216 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
       TileWalk walk;
       walk.init();
       int b, m, n, by, bx, cur_key = -1;
-      uint32_t a_uses = 0, bs = 0, i = 0;
+      uint32_t a_par = 0;                    // parity of the A-full phase to wait for next
+      uint32_t st = 0, ph = 0;
+      uint32_t i = 0;                        // tile counter: accumulator i & 1, its use number i >> 1
+      const uint32_t a_lo = desc_lo(sA), b_lo = desc_lo(sB);
       while (walk.next(p, b, m, n, by, bx)) {
         const int key = b * p.MT + m;
         if (key != cur_key) {
-          mbar_wait(bar_a_full, a_uses & 1);
-          ++a_uses;
+          mbar_wait(bar_a_full, a_par);
+          a_par ^= 1;
           cur_key = key;
         }
-        const uint32_t acc = i & 1, use = i >> 1;
+        const uint32_t acc = i & 1;
+        mbar_wait(bar_t_empty + 8 * acc, ((i >> 1) & 1) ^ 1);
         ++i;
-        mbar_wait(bar_t_empty + 8 * acc, (use & 1) ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BN;
-        for (int kb = 0; kb < p.KB; ++kb, ++bs) {
-          const uint32_t st = bs % p.stages, ph = (bs / p.stages) & 1;
+        for (int kb = 0; kb < p.KB; ++kb) {
           mbar_wait(bar_b_full + 8 * st, ph);
           tc_fence_after();
+          const uint32_t al = a_lo + ((kb * A_KB_BYTES) >> 4), bl = b_lo + ((st * B_ST_BYTES) >> 4);
 #pragma unroll
-          for (int k = 0; k < BK / UMMA_K; ++k) {
-            const uint64_t ad = umma_desc_sw128(sA + kb * A_KB_BYTES + k * (UMMA_K * 2));
-            const uint64_t bd = umma_desc_sw128(sB + st * B_ST_BYTES + k * (UMMA_K * 2));
-            umma_bf16(d_tmem, ad, bd, IDESC_BF16, (kb | k) != 0);
-          }
+          for (int k = 0; k < BK / UMMA_K; ++k)
+            umma_bf16(d_tmem, desc_make(al + k * ((UMMA_K * 2) >> 4)), desc_make(bl + k * ((UMMA_K * 2) >> 4)),
+                      IDESC_BF16, (kb | k) != 0);
           umma_commit(bar_b_empty + 8 * st);   // frees the B stage when these MMAs retire
+          if (++st == (uint32_t)p.stages) { st = 0; ph ^= 1; }
         }
         umma_commit(bar_t_full + 8 * acc);     // accumulator ready
         if (walk.a_changes(b, m)) umma_commit(bar_a_empty);   // last use of this A operand
       }
     }
   } else {
-    // ===================================================== epilogue (4 warps)
+    // ===================================================== epilogue (2 groups x 4 warps)
     const int quarter = warp & 3;                 // TMEM lanes [32*quarter, +32)
-    const uint32_t sbuf = sStage + (warp - EPI_WARP0) * stage_bytes_per_warp<VolT>();   // level-0 step buffer
-    const uint32_t pbuf = sbuf + STEP_BYTES;                                            // levels 1..3
+    const int group = (warp - EPI_WARP0) >> 2;    // block columns 16*group .. +15
+    const uint32_t sbuf = sStage + (warp - EPI_WARP0) * STAGE_BYTES_PER_WARP;   // level-0 step buffer
+    const uint32_t lbuf = sbuf + STEP_BYTES;                                    // level-1 buffer
     const int L = p.num_levels;
-    // per-lane constants of the staging buffers
-    const uint32_t st_base = (sbuf + lane * 256) | ((lane & 7) << 4);    // write: unit u at st_base ^ (u << 4)
-    const uint32_t pb_base = pbuf + lane * (S::NU * 16);                 // write: pooled unit u at pb_base + 16 u
-    const int u16 = lane & 15, hi = lane >> 4;                           // read-back of a step: unit, query parity
-    const uint32_t ld_base = (sbuf + hi * 256) | ((u16 ^ hi) << 4);
-    const int l0_tile = ES == 2 ? (u16 >> 2) : (u16 >> 1);               // tile (inside the chunk) of unit u16
-    constexpr int U1 = S::L1_UNITS, U2 = S::L2_UNITS;
-    const int u1 = lane % U1, sub1 = lane / U1, u2 = lane % U2, sub2 = lane / U2;
-    const uint32_t ld1 = pbuf + (sub1 * S::NU + u1) * 16;
-    const int l2_tile = ES == 2 ? 0 : (u2 >> 1), l2_row = ES == 2 ? u2 : (u2 & 1);
-    const uint32_t ld2 = pbuf + (sub2 * S::NU + U1 + (ES == 2 ? u2 : l2_row + 2 * l2_tile)) * 16;
+    // per-lane constants of the staging buffers (see flush128 / flush64)
+    const uint32_t st_base = (sbuf + lane * 128) | ((lane & 7) << 4);           // write: unit u at st_base ^ (u << 4)
+    const int u8 = lane & 7, sub4 = lane >> 3;
+    const uint32_t ld_base = (sbuf + sub4 * 128) | ((u8 ^ sub4) << 4);
+    const int l0_tile = ES == 2 ? (u8 >> 2) : (u8 >> 1);                        // tile (of the group's) holding unit u8
+    const int l0_off = ES == 2 ? u8 * 16 : (u8 >> 1) * 64 + (u8 & 1) * 16;      // its byte offset in the chunk
+    // level 1: bf16 = 4 units (one tile) per query, 64-byte rows; fp32 = 8 units (two tiles), 128-byte rows
+    const uint32_t l1_st = ES == 2 ? ((lbuf + lane * 64) | (((lane >> 1) & 3) << 4)) : ((lbuf + lane * 128) | ((lane & 7) << 4));
+    const int u4 = lane & 3, sub8 = lane >> 2;
+    const uint32_t l1_ld = ES == 2 ? (lbuf + sub8 * 64 + ((u4 ^ ((sub8 >> 1) & 3)) << 4)) : ((lbuf + sub4 * 128) | ((u8 ^ sub4) << 4));
+    const uint64_t pol_out = l2_policy_evict_first();
 
     TileWalk walk;
     walk.init();
     int b, m, n, by, bx;
     uint32_t i = 0;
     while (walk.next(p, b, m, n, by, bx)) {
-      const int x0 = bx * TB_W, y0 = by * TB_H;
-      const int qw = m * BM + quarter * 32;            // first query of this warp
-      const uint32_t acc = i & 1, use = i >> 1;
+      const uint32_t acc = i & 1, t_par = (i >> 1) & 1;
       ++i;
+      const int x0 = bx * TB_W, y0 = by * TB_H;
+      const int xg = x0 + group * GW;                  // first map column of this group's sub-block
+      const int qw = m * BM + quarter * 32;            // first query of this warp
       const long long slab_q0 = (long long)b * p.N + qw;    // slab index of this warp's first query
       const int nq = min(32, p.N - qw);                     // valid queries of this warp (may be <= 0)
 
-      // valid pooled cells of this block (floor rule of avg_pool2d; the rest is padding -> 0)
-      const int nvx1 = p.Wl[1] - (x0 >> 1), nvy1 = p.Hl[1] - (y0 >> 1);
-      const int nvx2 = p.Wl[2] - (x0 >> 2), nvy2 = p.Hl[2] - (y0 >> 2);
-      const int nvx3 = p.Wl[3] - (x0 >> 3), nvy3 = p.Hl[3] - (y0 >> 3);
-      const bool edge = (L > 1 && (nvx1 < 16 || nvy1 < 4)) || (L > 2 && (nvx2 < 8 || nvy2 < 2)) ||
-                        (L > 3 && (nvx3 < 4 || nvy3 < 1));
-      // level-0 chunk of this block: tiles tx0 .. tx0 + L0_TILES - 1 of tile rows (y0 >> 2), (y0 >> 2) + 1
-      const int tx0 = x0 / S::TW;
-      const int nt0 = min(S::L0_TILES, p.tiles_x[0] - tx0);
-      const bool full0 = nq == 32 && nt0 == S::L0_TILES;
+      // valid pooled cells of this sub-block (floor rule of avg_pool2d; the rest is padding -> 0)
+      const int nvx1 = p.Wl[1] - (xg >> 1), nvy1 = p.Hl[1] - (y0 >> 1);
+      const int nvx2 = p.Wl[2] - (xg >> 2), nvy2 = p.Hl[2] - (y0 >> 2);
+      const int nvx3 = p.Wl[3] - (xg >> 3), nvy3 = p.Hl[3] - (y0 >> 3);
+      const bool edge = (L > 1 && (nvx1 < 8 || nvy1 < 4)) || (L > 2 && (nvx2 < 4 || nvy2 < 2)) ||
+                        (L > 3 && (nvx3 < 2 || nvy3 < 1));
+      // level-0 chunk of this group: tiles txg .. txg + L0_GT - 1 of tile rows (y0 >> 2), (y0 >> 2) + 1
+      const int txg = xg / S::TW;
+      const int nt0 = min(S::L0_GT, p.tiles_x[0] - txg);
+      const bool full0 = nq == 32 && nt0 == S::L0_GT;
       const long long slab0B = p.slab[0] * ES;
-      char *g0 = (char *)p.lvl[0] + ((long long)(y0 >> 2) * p.tiles_x[0] + tx0) * 64 + (slab_q0 + hi) * slab0B +
-                 (ES == 2 ? u16 * 16 : (u16 >> 1) * 64 + (u16 & 1) * 16);
+      char *g0 = (char *)p.lvl[0] + ((long long)(y0 >> 2) * p.tiles_x[0] + txg) * 64 + (slab_q0 + sub4) * slab0B + l0_off;
       const long long tile_row0B = (long long)p.tiles_x[0] * 64;
 
-      mbar_wait(bar_t_full + 8 * acc, use & 1);
+      // ---- accumulator -> registers, then hand it back at once
+      mbar_wait(bar_t_full + 8 * acc, t_par);
       tc_fence_after();
-      const uint32_t taddr = tmem_base + acc * BN + ((uint32_t)(quarter * 32) << 16);
+      const uint32_t taddr = tmem_base + acc * BN + group * GW + ((uint32_t)(quarter * 32) << 16);
+      uint32_t raw[8][GW];
+#pragma unroll
+      for (int r = 0; r < 8; ++r) tmem_ld16(taddr + r * TB_W, raw[r]);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_t_empty + 8 * acc);
 
-      float p1prev[16], p2prev[8];
+      float p1prev[8], p2prev[4];
 #pragma unroll
       for (int rp = 0; rp < 4; ++rp) {
-        uint32_t r0[32], r1[32];
-        tmem_ld32(taddr + (2 * rp) * 32, r0);
-        tmem_ld32(taddr + (2 * rp + 1) * 32, r1);
-        tmem_ld_wait();
-        if (rp == 3) {
-          // all TMEM reads of this tile are done: hand the accumulator back
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(bar_t_empty + 8 * acc);
-        }
-        float v0[32], v1[32], p1[16];
+        float v0[GW], v1[GW], p1[8];
 #pragma unroll
-        for (int k = 0; k < 32; ++k) {
-          v0[k] = __uint_as_float(r0[k]);
-          v1[k] = __uint_as_float(r1[k]);
+        for (int k = 0; k < GW; ++k) {
+          v0[k] = __uint_as_float(raw[2 * rp][k]);
+          v1[k] = __uint_as_float(raw[2 * rp + 1][k]);
           if (SCALE) { v0[k] *= p.scale; v1[k] *= p.scale; }
         }
         // ---- level 0 units of block rows 2rp, 2rp+1
         if (ES == 2) {
           const int r = (2 * rp) & 3;                    // row inside the tile
 #pragma unroll
-          for (int k = 0; k < 4; ++k) {
+          for (int k = 0; k < 2; ++k) {
             put_unit<VolT>(st_base ^ ((k * 4 + r) << 4), v0 + 8 * k);
             put_unit<VolT>(st_base ^ ((k * 4 + r + 1) << 4), v1 + 8 * k);
           }
         } else {
 #pragma unroll
-          for (int k = 0; k < 8; ++k) {
+          for (int k = 0; k < 4; ++k) {
             put_unit<VolT>(st_base ^ ((k * 2) << 4), v0 + 4 * k);
             put_unit<VolT>(st_base ^ ((k * 2 + 1) << 4), v1 + 4 * k);
           }
         }
         // ---- pooled levels, from the fp32 values
 #pragma unroll
-        for (int k = 0; k < 16; ++k) p1[k] = 0.25f * ((v0[2 * k] + v0[2 * k + 1]) + (v1[2 * k] + v1[2 * k + 1]));
+        for (int k = 0; k < 8; ++k) p1[k] = 0.25f * ((v0[2 * k] + v0[2 * k + 1]) + (v1[2 * k] + v1[2 * k + 1]));
         if (edge) {
 #pragma unroll
-          for (int k = 0; k < 16; ++k) p1[k] = (k < nvx1 && rp < nvy1) ? p1[k] : 0.f;
+          for (int k = 0; k < 8; ++k) p1[k] = (k < nvx1 && rp < nvy1) ? p1[k] : 0.f;
         }
         if (L > 1) {
-#pragma unroll
-          for (int k = 0; k < 16 / S::TW; ++k) put_unit<VolT>(pb_base + (k * 4 + rp) * 16, p1 + S::TW * k);
+          // level-1 row rp of the sub-block: bf16 one unit (row rp of its tile), fp32 two (tiles 0, 1)
+          if (ES == 2) {
+            put_unit<VolT>(l1_st ^ (rp << 4), p1);
+          } else {
+            put_unit<VolT>(l1_st ^ (rp << 4), p1);
+            put_unit<VolT>(l1_st ^ ((4 + rp) << 4), p1 + 4);
+          }
         }
         if (rp & 1) {
-          float p2[8];
+          // ---- level-2 row rp >> 1: 4 cells, straight from this thread's registers
+          float p2[4];
 #pragma unroll
-          for (int k = 0; k < 8; ++k)
+          for (int k = 0; k < 4; ++k)
             p2[k] = 0.25f * ((p1prev[2 * k] + p1prev[2 * k + 1]) + (p1[2 * k] + p1[2 * k + 1]));
           if (edge) {
 #pragma unroll
-            for (int k = 0; k < 8; ++k) p2[k] = (k < nvx2 && (rp >> 1) < nvy2) ? p2[k] : 0.f;
+            for (int k = 0; k < 4; ++k) p2[k] = (k < nvx2 && (rp >> 1) < nvy2) ? p2[k] : 0.f;
           }
-          if (L > 2) {
-            put_unit<VolT>(pb_base + (U1 + (rp >> 1)) * 16, p2);
-            if (ES == 4) put_unit<VolT>(pb_base + (U1 + 2 + (rp >> 1)) * 16, p2 + 4);
+          const int x2 = xg >> 2;                        // first level-2 column of the sub-block
+          if (L > 2 && lane < nq && (y0 >> 4) < p.tiles_y[2] && x2 / S::TW < p.tiles_x[2]) {
+            char *g2 = (char *)p.lvl[2] + ((long long)(y0 >> 4) * p.tiles_x[2] + x2 / S::TW) * 64 +
+                       (slab_q0 + lane) * p.slab[2] * ES + (((y0 >> 2) & 3) + (rp >> 1)) * 16 + (x2 % S::TW) * ES;
+            if (ES == 2) stg8_hint(g2, pack_bf16(p2[0], p2[1]), pack_bf16(p2[2], p2[3]), pol_out);
+            else stg16_hint(g2, make_uint4(__float_as_uint(p2[0]), __float_as_uint(p2[1]), __float_as_uint(p2[2]),
+                                           __float_as_uint(p2[3])), pol_out);
           }
           if (rp == 3) {
-            float p3[8];
+            // ---- level 3: 2 cells
+            float p3[2];
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
+            for (int k = 0; k < 2; ++k) {
               const float a = 0.25f * ((p2prev[2 * k] + p2prev[2 * k + 1]) + (p2[2 * k] + p2[2 * k + 1]));
               p3[k] = (!edge || (k < nvx3 && 0 < nvy3)) ? a : 0.f;
-              p3[4 + k] = 0.f;
             }
-            if (L > 3) put_unit<VolT>(pb_base + (U1 + U2) * 16, p3);
+            const int x3 = xg >> 3;
+            if (L > 3 && lane < nq && (y0 >> 5) < p.tiles_y[3] && x3 / S::TW < p.tiles_x[3]) {
+              char *g3 = (char *)p.lvl[3] + ((long long)(y0 >> 5) * p.tiles_x[3] + x3 / S::TW) * 64 +
+                         (slab_q0 + lane) * p.slab[3] * ES + ((y0 >> 3) & 3) * 16 + (x3 % S::TW) * ES;
+              if (ES == 2) {
+                stg4_hint(g3, pack_bf16(p3[0], p3[1]), pol_out);
+                // a bf16 tile row holds the cells of two blocks; with no block to the right, its
+                // cells 4..7 are padding columns and must read as zero
+                if (group == 1 && !(bx & 1) && bx + 1 >= p.nbx) stg8_hint(g3 + 4, 0u, 0u, pol_out);
+              } else {
+                stg8_hint(g3, __float_as_uint(p3[0]), __float_as_uint(p3[1]), pol_out);
+              }
+            }
           } else {
 #pragma unroll
-            for (int k = 0; k < 8; ++k) p2prev[k] = p2[k];
+            for (int k = 0; k < 4; ++k) p2prev[k] = p2[k];
           }
         } else {
 #pragma unroll
-          for (int k = 0; k < 16; ++k) p1prev[k] = p1[k];
+          for (int k = 0; k < 8; ++k) p1prev[k] = p1[k];
         }
 
         // ---- a level-0 step is complete: read it back query by query, coalesced stores
         if (ES == 4 || (rp & 1)) {
           __syncwarp();
           // bf16: step = one row of tiles; fp32: step = two of the four rows of a row of tiles
-          const int trow = ES == 2 ? (rp >> 1) : (rp >> 1);
-          const int half = ES == 2 ? 0 : (rp & 1) * 32;
-          if ((y0 >> 2) + trow < p.tiles_y[0] && nt0 > 0) {
-            char *g = g0 + trow * tile_row0B + half;
-            if (full0) flush_step<true>(ld_base, g, 2 * slab0B, hi, nq, true);
-            else flush_step<false>(ld_base, g, 2 * slab0B, hi, nq, l0_tile < nt0);
+          if ((y0 >> 2) + (rp >> 1) < p.tiles_y[0] && nt0 > 0) {
+            char *g = g0 + (rp >> 1) * tile_row0B + (ES == 2 ? 0 : (rp & 1) * 32);
+            if (full0) flush128<true>(ld_base, g, 4 * slab0B, sub4, nq, true, pol_out);
+            else flush128<false>(ld_base, g, 4 * slab0B, sub4, nq, l0_tile < nt0, pol_out);
           }
           __syncwarp();
         }
       }
 
-      // ---- levels 1..3 of this block
-      __syncwarp();
+      // ---- level-1 cells of the sub-block
       if (L > 1) {
-        const int ty = y0 >> 3, tx1 = (x0 >> 1) / S::TW;
-        const int nt = min(U1 / 4, p.tiles_x[1] - tx1);
-        if (ty < p.tiles_y[1] && nt > 0) {
-          const long long slabB = p.slab[1] * ES;
-          char *g = (char *)p.lvl[1] + ((long long)ty * p.tiles_x[1] + tx1) * 64 + (slab_q0 + sub1) * slabB + u1 * 16;
-          if (nq == 32 && nt == U1 / 4) flush_pooled<U1, true>(ld1, S::NU * 16, g, slabB, sub1, nq, true);
-          else flush_pooled<U1, false>(ld1, S::NU * 16, g, slabB, sub1, nq, (u1 >> 2) < nt);
-        }
-      }
-      if (L > 2) {
-        const int ty = y0 >> 4, tx2 = (x0 >> 2) / S::TW;
-        const int row0 = (y0 >> 2) & 3;                       // first of the block's two rows inside the tile
-        if (ty < p.tiles_y[2]) {
-          const long long slabB = p.slab[2] * ES;
-          char *g = (char *)p.lvl[2] + ((long long)ty * p.tiles_x[2] + tx2) * 64 + (slab_q0 + sub2) * slabB +
-                    l2_tile * 64 + (row0 + l2_row) * 16;
-          flush_pooled<U2, false>(ld2, S::NU * 16, g, slabB, sub2, nq, tx2 + l2_tile < p.tiles_x[2]);
-        }
-      }
-      if (L > 3) {
-        const int ty = y0 >> 5, tx = (x0 >> 3) / S::TW;
-        const int row = (y0 >> 3) & 3;
-        if (ty < p.tiles_y[3] && tx < p.tiles_x[3] && lane < nq) {
-          char *dst = (char *)p.lvl[3] + ((long long)ty * p.tiles_x[3] + tx) * 64 + (slab_q0 + lane) * p.slab[3] * ES +
-                      row * 16;
-          const uint4 val = lds16(pb_base + (U1 + U2) * 16);
-          if (ES == 4) {
-            *reinterpret_cast<uint4 *>(dst) = val;
+        const int tx1 = (xg >> 1) / S::TW;
+        const int nt1 = min(S::L1_GT, p.tiles_x[1] - tx1);
+        if ((y0 >> 3) < p.tiles_y[1] && nt1 > 0) {
+          const long long slab1B = p.slab[1] * ES;
+          char *g1 = (char *)p.lvl[1] + ((long long)(y0 >> 3) * p.tiles_x[1] + tx1) * 64;
+          if (ES == 2) {
+            g1 += (slab_q0 + sub8) * slab1B + u4 * 16;
+            if (nq == 32) flush64<true>(l1_ld, g1, 8 * slab1B, sub8, nq, true, pol_out);
+            else flush64<false>(l1_ld, g1, 8 * slab1B, sub8, nq, true, pol_out);
           } else {
-            // 4 cells = 8 bytes: the left or right half of a tile row.  The left writer also
-            // zeroes the right half when no block to its right exists (padding columns).
-            const bool right = (bx & 1) != 0;
-            if (right) *reinterpret_cast<uint2 *>(dst + 8) = make_uint2(val.x, val.y);
-            else if (bx + 1 < p.nbx) *reinterpret_cast<uint2 *>(dst) = make_uint2(val.x, val.y);
-            else *reinterpret_cast<uint4 *>(dst) = val;
+            g1 += (slab_q0 + sub4) * slab1B + u8 * 16;       // unit u8 = tile u8 >> 2, row u8 & 3
+            if (nq == 32 && nt1 == 2) flush128<true>(l1_ld, g1, 4 * slab1B, sub4, nq, true, pol_out);
+            else flush128<false>(l1_ld, g1, 4 * slab1B, sub4, nq, (u8 >> 2) < nt1, pol_out);
           }
         }
+        __syncwarp();
       }
-      __syncwarp();
     }
   }
 
@@ -625,9 +655,9 @@ int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, con
   RC_CUDA(cudaGetDevice(&dev));
   RC_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   RC_CUDA(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
-  const size_t fixed = (size_t)p.KB * A_KB_BYTES + 4 * (size_t)stage_bytes_per_warp<VolT>() + 256 + 1024;
+  const size_t fixed = (size_t)p.KB * A_KB_BYTES + (size_t)EPI_WARPS * STAGE_BYTES_PER_WARP + 256 + 1024;
   p.stages = 0;
-  for (int st = 4; st >= 2; --st)
+  for (int st = MAX_STAGES; st >= 2; --st)
     if (fixed + (size_t)st * B_ST_BYTES <= (size_t)max_smem) {
       p.stages = st;
       break;
@@ -638,9 +668,9 @@ int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, con
   }
   const size_t smem = fixed + (size_t)p.stages * B_ST_BYTES;
 
-  // pairs per group: about two query blocks' worth of tiles per CTA and group
+  // pairs per group: about one query block's worth of tiles per CTA and group
   const long long tpp = (long long)p.MT * p.NT;
-  long long gp = (2LL * p.NT * sms + tpp - 1) / tpp;
+  long long gp = ((long long)p.NT * sms + tpp - 1) / tpp;
   if (gp < 1) gp = 1;
   if (gp > B) gp = B;
   p.group_pairs = (int)gp;
