@@ -46,6 +46,31 @@ def peaks():
     return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
 
 
+def ncu_traffic(kernel, batch, storage):
+    """DRAM bytes per launch of `kernel` from the committed ncu capture (profiles/traffic.json),
+    or None when the capture was taken on another configuration."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if not os.path.exists(p):
+        return None
+    ent = json.load(open(p)).get(kernel)
+    if not ent or ent.get("pairs") != batch or ent.get("storage") != storage:
+        return None
+    return ent["dram_bytes_per_launch"]
+
+
+def write_only_gbs(device):
+    """HBM bandwidth of a pure write stream (fill of 1 GiB), measured live: the ceiling of the volume
+    build, which writes 16x more than it reads.  (The copy figure in MEASURED_PEAKS.json is read + write.)"""
+    buf = torch.empty(1 << 29, dtype=torch.bfloat16, device=device)
+    best = 1e9
+    for i in range(6):
+        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+        e0.record(); buf.fill_(1.0); e1.record(); torch.cuda.synchronize()
+        if i:
+            best = min(best, e0.elapsed_time(e1))
+    return (1 << 30) / best / 1e6
+
+
 def make_inputs(batch, device, seed):
     """Seeded synthetic features and 12 coordinate fields (grid + N(0, 5^2) flow)."""
     g = torch.Generator(device="cpu").manual_seed(seed)
@@ -248,18 +273,22 @@ def main():
     build_gbs = build_bytes / (build_avg * 1e-3) / 1e9
     build_tf = B * BUILD_FLOPS / (build_avg * 1e-3) / 1e12
     lookups_dominate = ITERS * look_avg >= build_avg
+    wr_gbs = write_only_gbs(device)
     if lookups_dominate:
         roof = {"kernel": "lookup_fwd_kernel", "bound": "hbm", "achieved": look_gbs, "peak": pk["hbm_gbs"], "unit": "GB/s",
-                "frac": look_gbs / pk["hbm_gbs"], "traffic": None, "peak_source": pk["source"],
+                "frac": look_gbs / pk["hbm_gbs"], "traffic": ncu_traffic("lookup_fwd_kernel", B, args.storage),
+                "peak_source": pk["source"],
                 "algorithmic_bytes_per_launch": look_bytes, "avg_launch_ms": look_avg}
     else:
         roof = {"kernel": "build_pyramid_tc_kernel(+pack)", "bound": "hbm", "achieved": build_gbs, "peak": pk["hbm_gbs"],
-                "unit": "GB/s", "frac": build_gbs / pk["hbm_gbs"], "traffic": None, "peak_source": pk["source"],
+                "unit": "GB/s", "frac": build_gbs / pk["hbm_gbs"],
+                "traffic": ncu_traffic("build_pyramid_tc_kernel", B, args.storage), "peak_source": pk["source"],
                 "algorithmic_bytes_per_launch": build_bytes, "avg_launch_ms": build_avg}
     kernels = {
         "lookup_fwd": {"avg_ms": look_avg, "GB/s": look_gbs, "frac_hbm": look_gbs / pk["hbm_gbs"], "share_of_step": ITERS * look_avg / (ITERS * look_avg + build_avg)},
         "build(pack+tcgen05)": {"avg_ms": build_avg, "GB/s": build_gbs, "frac_hbm": build_gbs / pk["hbm_gbs"], "TFLOP/s": build_tf,
-                                "frac_tensor": build_tf / pk["bf16_tflops_sustained"], "share_of_step": build_avg / (ITERS * look_avg + build_avg)},
+                                "frac_tensor": build_tf / pk["bf16_tflops_sustained"], "share_of_step": build_avg / (ITERS * look_avg + build_avg),
+                                "write_only_hbm_GB/s_measured": wr_gbs, "frac_of_write_only": build_gbs / wr_gbs},
     }
 
     # ---- end to end through the public API from pinned host buffers

@@ -1,0 +1,86 @@
+"""RAFT end-to-end harness around the frozen reference sub-networks (test infrastructure).
+
+The three networks (feature encoder, context encoder, update block) are the reference's own
+modules, traced by oracle/make_ref_modules.py; this file re-states only the control flow of
+RAFT.forward (core/raft.py:86-144) so that the correlation block is a parameter:
+
+    corr_cls(fmap1, fmap2, radius=4) -> corr_fn;  corr_fn(coords1) -> [B, 324, H/8, W/8]
+
+which is exactly how the reference uses CorrBlock / AlternateCorrBlock (core/raft.py:104-107,
+:124).  Used by the GPU end-to-end test, bench.py's extras and nothing else.
+"""
+from __future__ import annotations
+
+import os
+
+import torch
+import torch.nn.functional as F
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REF_DIR = os.path.join(HERE, "_ref")
+FILES = ("raft_basic_fnet.pt", "raft_basic_cnet.pt", "raft_basic_update.pt")
+HDIM = CDIM = 128   # core/raft.py:35-36
+
+
+def available() -> bool:
+    return all(os.path.exists(os.path.join(REF_DIR, f)) for f in FILES)
+
+
+def load(device):
+    """(fnet, cnet, update_block) TorchScript modules on `device`."""
+    return tuple(torch.jit.load(os.path.join(REF_DIR, f), map_location=device).eval() for f in FILES)
+
+
+def coords_grid(batch, ht, wd, device):
+    ys, xs = torch.meshgrid(torch.arange(ht, device=device), torch.arange(wd, device=device), indexing="ij")
+    return torch.stack([xs, ys], dim=0).float()[None].repeat(batch, 1, 1, 1)   # core/utils/utils.py:74-77
+
+
+def upsample_flow(flow, mask):
+    """convex 8x upsampling, core/raft.py:72-83"""
+    N, _, H, W = flow.shape
+    mask = torch.softmax(mask.view(N, 1, 9, 8, 8, H, W), dim=2)
+    up = F.unfold(8 * flow, [3, 3], padding=1).view(N, 2, 9, 1, 1, H, W)
+    up = torch.sum(mask * up, dim=2).permute(0, 1, 4, 2, 5, 3)
+    return up.reshape(N, 2, 8 * H, 8 * W)
+
+
+class TorchCorrBlock:
+    """The reference CorrBlock's arithmetic (torch library calls, oracle/torch_port.py) on whatever
+    device the features live on: the 'reference through stock torch' arm of the comparison."""
+
+    def __init__(self, fmap1, fmap2, num_levels=4, radius=4):
+        from . import torch_port as P
+        self._P = P
+        self.radius = radius
+        self.pyr = P.build_pyramid(fmap1, fmap2, num_levels)
+
+    def __call__(self, coords):
+        return self._P.lookup(self.pyr, coords, self.radius)
+
+
+@torch.no_grad()
+def raft_forward(nets, image1, image2, iters=12, corr_cls=TorchCorrBlock, last_only=True):
+    """RAFT.forward(test_mode=True) (core/raft.py:86-144) -> (flow_low, flow_up)."""
+    fnet, cnet, update = nets
+    image1 = (2 * (image1 / 255.0) - 1.0).contiguous()
+    image2 = (2 * (image2 / 255.0) - 1.0).contiguous()
+    B = image1.shape[0]
+    # the reference feeds [image1, image2] as a list, which its encoder concatenates on the batch
+    # axis and splits again (core/extractor.py:171-174, :189-190)
+    fmaps = fnet(torch.cat([image1, image2], dim=0)).float()
+    fmap1, fmap2 = fmaps[:B], fmaps[B:]
+    corr_fn = corr_cls(fmap1, fmap2, radius=4)
+    net, inp = torch.split(cnet(image1), [HDIM, CDIM], dim=1)
+    net, inp = torch.tanh(net), torch.relu(inp)
+    H8, W8 = image1.shape[2] // 8, image1.shape[3] // 8
+    coords0 = coords_grid(B, H8, W8, image1.device)
+    coords1 = coords0.clone()
+    flow_up = None
+    for it in range(iters):
+        corr = corr_fn(coords1)
+        net, up_mask, delta = update(net, inp, corr, coords1 - coords0)
+        coords1 = coords1 + delta
+        if not last_only or it == iters - 1:
+            flow_up = upsample_flow(coords1 - coords0, up_mask)   # the reference upsamples every iteration
+    return coords1 - coords0, flow_up

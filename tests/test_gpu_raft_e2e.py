@@ -1,0 +1,59 @@
+"""End-to-end check of BASELINE config 1: RAFT-basic, random-init weights (seed 1234), one
+440x1024 pair, 12 iterations -- the reference's sub-networks (frozen by
+oracle/make_ref_modules.py) around (a) the reference CorrBlock's torch arithmetic and (b) this
+library's correlation blocks.  north_star tolerance: mean end-point-error delta of the final
+flow <= 0.01 px against the fp32 reference.
+"""
+from functools import partial
+
+import pytest
+import torch
+
+from oracle import raft_harness as Hn
+
+pytestmark = [pytest.mark.gpu,
+              pytest.mark.skipif(not Hn.available(), reason="oracle/_ref/*.pt not built (needs the reference checkout)")]
+
+R = pytest.importorskip("raft_stir_b200")
+
+
+def _inputs(B, H, W, dev):
+    g = torch.Generator(device="cpu").manual_seed(0)
+    im1 = torch.rand(B, 3, H, W, generator=g) * 255.0
+    im2 = torch.rand(B, 3, H, W, generator=g) * 255.0
+    return im1.to(dev), im2.to(dev)
+
+
+def _epe(a, b):
+    return torch.sqrt(((a - b) ** 2).sum(dim=1)).mean().item()
+
+
+@pytest.fixture(scope="module")
+def reference_run():
+    if not torch.cuda.is_available():
+        pytest.fail("GPU test selected but no CUDA device is visible")
+    dev = torch.device("cuda:0")
+    nets = Hn.load(dev)
+    im1, im2 = _inputs(1, 440, 1024, dev)
+    low, up = Hn.raft_forward(nets, im1, im2, iters=12, corr_cls=Hn.TorchCorrBlock)
+    assert torch.isfinite(up).all()
+    return nets, im1, im2, low, up
+
+
+def test_flow_with_bf16_tensor_core_volume(reference_run):
+    nets, im1, im2, low, up = reference_run
+    _, got = Hn.raft_forward(nets, im1, im2, iters=12, corr_cls=R.CorrBlock)      # defaults: bf16 storage, tcgen05 build
+    d = _epe(got, up)
+    assert d <= 0.01, f"mean EPE delta {d:.5f} px > 0.01 px (mean |flow| {up.norm(dim=1).mean().item():.2f} px)"
+
+
+def test_flow_with_fp32_volume(reference_run):
+    nets, im1, im2, low, up = reference_run
+    _, got = Hn.raft_forward(nets, im1, im2, iters=12, corr_cls=partial(R.CorrBlock, storage="fp32", math="fp32"))
+    assert _epe(got, up) <= 1e-3
+
+
+def test_flow_with_on_the_fly_correlation(reference_run):
+    nets, im1, im2, low, up = reference_run
+    _, got = Hn.raft_forward(nets, im1, im2, iters=12, corr_cls=R.AlternateCorrBlock)
+    assert _epe(got, up) <= 1e-3

@@ -1,0 +1,52 @@
+#!/usr/bin/env python3
+"""Full RAFT-basic forward (BASELINE config 1: 440x1024, 12 iterations, random-init weights) on one
+GPU: the reference's frozen sub-networks (oracle/_ref, see oracle/make_ref_modules.py) around
+(a) the reference CorrBlock's torch ops on the GPU and (b) this library's blocks.  Prints one
+JSON line: frame pairs per second and the end-point-error deltas.  Not part of bench.py (whose
+subject is the correlation path alone); the encoders and the GRU are the reference's, untouched.
+"""
+import json
+import os
+import sys
+from functools import partial
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import raft_stir_b200 as R          # noqa: E402
+from oracle import raft_harness as Hn   # noqa: E402
+
+
+def main():
+    B = int(sys.argv[1]) if len(sys.argv) > 1 else 1
+    dev = torch.device("cuda:0")
+    nets = Hn.load(dev)
+    g = torch.Generator(device="cpu").manual_seed(0)
+    im1 = (torch.rand(B, 3, 440, 1024, generator=g) * 255).to(dev)
+    im2 = (torch.rand(B, 3, 440, 1024, generator=g) * 255).to(dev)
+
+    def timeit(cls, reps):
+        Hn.raft_forward(nets, im1, im2, 12, cls)
+        torch.cuda.synchronize()
+        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            out = Hn.raft_forward(nets, im1, im2, 12, cls)
+        e1.record(); torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps, out[1]
+
+    res = {"config": f"RAFT-basic random-init, {B} pair(s) 440x1024, 12 iters, fp32 networks"}
+    ms_ref, up_ref = timeit(Hn.TorchCorrBlock, 3)
+    res["torch_corrblock_on_gpu"] = {"ms": ms_ref, "pairs_per_s": 1e3 * B / ms_ref}
+    for name, cls in (("ours_bf16_tensor_core", R.CorrBlock),
+                      ("ours_fp32", partial(R.CorrBlock, storage="fp32", math="fp32")),
+                      ("ours_on_the_fly", R.AlternateCorrBlock)):
+        ms, up = timeit(cls, 5)
+        epe = torch.sqrt(((up - up_ref) ** 2).sum(1)).mean().item()
+        res[name] = {"ms": ms, "pairs_per_s": 1e3 * B / ms, "mean_epe_delta_px": epe}
+    res["mean_flow_px"] = up_ref.norm(dim=1).mean().item()
+    print(json.dumps(res))
+
+
+if __name__ == "__main__":
+    main()
