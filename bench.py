@@ -397,6 +397,31 @@ def run_extras(R, device, args, pk):
             loss = sum(blk(c).sum() for c in cc)
             loss.backward()
         out["chairs_b10_fwd_bwd_ms"] = timeit(train_step, 5)
+        # the two backward kernels alone, same shape: 12 lookup backwards into one gradient pyramid, then the build backward
+        with torch.no_grad():
+            blk = R.CorrBlock(a1.detach(), a2.detach(), LEVELS, RADIUS, storage=args.storage)
+            go = torch.randn(Bc, LEVELS * (2 * RADIUS + 1) ** 2, Hc, Wc, device=device)
+            blk._lookup_backward(cc[0], go, True, False)
+            ms = timeit(lambda: blk._lookup_backward(cc[0], go, True, False), 20)
+            nq = Bc * Hc * Wc
+            bwd_bytes = nq * (LEVELS * (2 * RADIUS + 1) ** 2 * 4 + 8 + LEVELS * (2 * RADIUS + 2) ** 2 * 4 * 2)
+            out["chairs_b10_lookup_bwd_ms"] = ms
+            out["chairs_b10_lookup_bwd_GB/s"] = bwd_bytes / (ms * 1e-3) / 1e9
+            out["chairs_b10_lookup_bwd_frac_hbm"] = out["chairs_b10_lookup_bwd_GB/s"] / pk["hbm_gbs"]
+        # STIR-scale video (config 4): one 1080x1920 pair, fmap 135x240
+        with torch.no_grad():
+            g = torch.Generator(device="cpu").manual_seed(11)
+            Hv, Wv = 135, 240
+            v1 = torch.randn(1, D, Hv, Wv, generator=g).to(device)
+            v2 = torch.randn(1, D, Hv, Wv, generator=g).to(device)
+            cv = R.coords_grid(1, Hv, Wv, device) + 5 * torch.randn(1, 2, Hv, Wv, device=device)
+            out["v1080_build_ms"] = timeit(lambda: R.CorrBlock(v1, v2, LEVELS, RADIUS, storage=args.storage), 3)
+            blk = R.CorrBlock(v1, v2, LEVELS, RADIUS, storage=args.storage)
+            out["v1080_lookup_ms"] = timeit(lambda: blk(cv), 20)
+            del blk
+            altv = R.AlternateCorrBlock(v1, v2, LEVELS, RADIUS)
+            out["v1080_alt_lookup_ms"] = timeit(lambda: altv(cv), 5)
+            out["v1080_note"] = "12 iterations: default = build + 12 lookups; on-the-fly = 12 alt lookups (no volume in memory)"
     except Exception as e:  # extras must never sink the headline
         out["error"] = f"{type(e).__name__}: {e}"
     return out

@@ -84,3 +84,40 @@ def raft_forward(nets, image1, image2, iters=12, corr_cls=TorchCorrBlock, last_o
         if not last_only or it == iters - 1:
             flow_up = upsample_flow(coords1 - coords0, up_mask)   # the reference upsamples every iteration
     return coords1 - coords0, flow_up
+
+
+def raft_forward_train(nets, image1, image2, iters=12, corr_cls=TorchCorrBlock):
+    """RAFT.forward(test_mode=False) (core/raft.py:86-144): the list of upsampled flow predictions, with
+    autograd history.  coords1 is detached every iteration exactly as the reference does (:123)."""
+    fnet, cnet, update = nets
+    image1 = (2 * (image1 / 255.0) - 1.0).contiguous()
+    image2 = (2 * (image2 / 255.0) - 1.0).contiguous()
+    B = image1.shape[0]
+    fmaps = fnet(torch.cat([image1, image2], dim=0)).float()
+    fmap1, fmap2 = fmaps[:B], fmaps[B:]
+    corr_fn = corr_cls(fmap1, fmap2, radius=4)
+    net, inp = torch.split(cnet(image1), [HDIM, CDIM], dim=1)
+    net, inp = torch.tanh(net), torch.relu(inp)
+    H8, W8 = image1.shape[2] // 8, image1.shape[3] // 8
+    coords0 = coords_grid(B, H8, W8, image1.device)
+    coords1 = coords0.clone()
+    preds = []
+    for _ in range(iters):
+        coords1 = coords1.detach()
+        corr = corr_fn(coords1)
+        net, up_mask, delta = update(net, inp, corr, coords1 - coords0)
+        coords1 = coords1 + delta
+        preds.append(upsample_flow(coords1 - coords0, up_mask))
+    return preds
+
+
+def sequence_loss(preds, flow_gt, valid, gamma=0.8, max_flow=400.0):
+    """train.py:47-72 (the loss only; metrics left out)."""
+    n = len(preds)
+    mag = torch.sum(flow_gt ** 2, dim=1).sqrt()
+    valid = (valid >= 0.5) & (mag < max_flow)
+    loss = 0.0
+    for i, p in enumerate(preds):
+        w = gamma ** (n - i - 1)
+        loss = loss + w * (valid[:, None] * (p - flow_gt).abs()).mean()
+    return loss

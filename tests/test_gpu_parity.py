@@ -356,3 +356,27 @@ def test_non_default_stream_and_noncontiguous_inputs():
         got = R.CorrBlock(f1, f2, storage="fp32", math="fp32")(c)
     s.synchronize()
     assert torch.equal(ref, got)
+
+
+def test_lookup_is_cuda_graph_capturable():
+    """The per-iteration call can be captured once and replayed (the natural way to run the 12-iteration
+    loop without launch gaps): no synchronisation, no legacy-stream work inside rc_lookup_fwd."""
+    rng = np.random.default_rng(3)
+    B, D, H, W = 2, 32, 24, 40
+    blk = R.CorrBlock(t(rng.standard_normal((B, D, H, W)).astype(np.float32)),
+                      t(rng.standard_normal((B, D, H, W)).astype(np.float32)), 4, 4)
+    coords = R.coords_grid(B, H, W, dev()) + 2.5
+    ref = blk(coords).clone()
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        blk(coords)                       # warm-up on the side stream (first-call attribute set-up)
+    torch.cuda.current_stream().wait_stream(s)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        out = blk(coords)
+    coords.add_(1.0)                      # new coordinates in the captured input buffer
+    graph.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(out, blk(coords))
+    assert not torch.equal(out, ref)

@@ -57,3 +57,24 @@ def test_flow_with_on_the_fly_correlation(reference_run):
     nets, im1, im2, low, up = reference_run
     _, got = Hn.raft_forward(nets, im1, im2, iters=12, corr_cls=R.AlternateCorrBlock)
     assert _epe(got, up) <= 1e-3
+
+
+def test_training_gradients_through_the_block():
+    """BASELINE config 5 in miniature: loss.backward() through the whole network with this library's
+    autograd-enabled CorrBlock (fp32) gives the parameter gradients the reference block's torch ops give."""
+    if not torch.cuda.is_available():
+        pytest.fail("GPU test selected but no CUDA device is visible")
+    dev = torch.device("cuda:0")
+    im1, im2 = _inputs(2, 160, 224, dev)
+    gt = torch.zeros(2, 2, 160, 224, device=dev)
+    valid = torch.ones(2, 160, 224, device=dev)
+    grads = []
+    for cls in (Hn.TorchCorrBlock, partial(R.CorrBlock, storage="fp32", math="fp32")):
+        nets = Hn.load(dev)
+        loss = Hn.sequence_loss(Hn.raft_forward_train(nets, im1, im2, 4, cls), gt, valid)
+        loss.backward()
+        grads.append(torch.cat([p.grad.flatten() for p in nets[0].parameters() if p.grad is not None]))
+    a, b = grads
+    assert a.numel() > 1000 and torch.isfinite(b).all()
+    rel = (a - b).norm() / a.norm()
+    assert rel < 2e-3, rel
