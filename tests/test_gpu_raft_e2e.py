@@ -59,22 +59,44 @@ def test_flow_with_on_the_fly_correlation(reference_run):
     assert _epe(got, up) <= 1e-3
 
 
+class _JitteredReference(Hn.TorchCorrBlock):
+    """The reference block with 1e-7 relative noise on its output: the yardstick for how much the rest
+    of the network amplifies a last-bit difference in the correlation features."""
+
+    def __call__(self, coords):
+        out = super().__call__(coords)
+        return out * (1 + 1e-7 * torch.randn_like(out))
+
+
 def test_training_gradients_through_the_block():
     """BASELINE config 5 in miniature: loss.backward() through the whole network with this library's
-    autograd-enabled CorrBlock (fp32) gives the parameter gradients the reference block's torch ops give."""
+    autograd-enabled CorrBlock (fp32).  The block itself matches torch autograd of the reference ops to
+    1e-6 (test_gpu_parity.py); the random-init network around it turns a 1e-7 difference in the
+    correlation features into a ~1e-2 difference in the parameter gradients (measured here with the
+    jittered reference), so that is the scale the comparison is made on."""
     if not torch.cuda.is_available():
         pytest.fail("GPU test selected but no CUDA device is visible")
     dev = torch.device("cuda:0")
     im1, im2 = _inputs(2, 160, 224, dev)
     gt = torch.zeros(2, 2, 160, 224, device=dev)
     valid = torch.ones(2, 160, 224, device=dev)
-    grads = []
-    for cls in (Hn.TorchCorrBlock, partial(R.CorrBlock, storage="fp32", math="fp32")):
-        nets = Hn.load(dev)
-        loss = Hn.sequence_loss(Hn.raft_forward_train(nets, im1, im2, 4, cls), gt, valid)
-        loss.backward()
-        grads.append(torch.cat([p.grad.flatten() for p in nets[0].parameters() if p.grad is not None]))
-    a, b = grads
-    assert a.numel() > 1000 and torch.isfinite(b).all()
-    rel = (a - b).norm() / a.norm()
-    assert rel < 2e-3, rel
+    old = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False
+    torch.manual_seed(0)
+    try:
+        grads, losses = [], []
+        for cls in (Hn.TorchCorrBlock, _JitteredReference, partial(R.CorrBlock, storage="fp32", math="fp32")):
+            nets = Hn.load(dev)
+            loss = Hn.sequence_loss(Hn.raft_forward_train(nets, im1, im2, 4, cls), gt, valid)
+            loss.backward()
+            losses.append(loss.item())
+            grads.append(torch.cat([p.grad.flatten() for p in nets[0].parameters() if p.grad is not None]))
+    finally:
+        torch.backends.cudnn.allow_tf32 = old
+    a, aj, b = grads
+    assert a.numel() > 1000 and torch.isfinite(b).all() and b.abs().max() > 0
+    assert abs(losses[2] - losses[0]) <= 1e-4 * abs(losses[0])
+    floor = ((a - aj).norm() / a.norm()).item()
+    rel = ((a - b).norm() / a.norm()).item()
+    cos = torch.nn.functional.cosine_similarity(a, b, dim=0).item()
+    assert cos > 0.999 and rel < 3 * floor + 2e-3, f"gradient difference {rel:.2e} (cos {cos:.5f}); 1e-7 jitter floor {floor:.2e}"
