@@ -1,7 +1,8 @@
 """This library's rc_alt_fwd / rc_alt_bwd against the REFERENCE'S OWN alt_cuda_corr extension,
 compiled unmodified from /root/reference/alt_cuda_corr by oracle/build_ref_ext.sh and shipped in
 oracle/_ref/.  Same tensors in (alt_cuda_corr/correlation.cpp:23-48), same lists out.  fp32: 1e-4.
-Skipped where the extension was not built."""
+The reference kernel reads channels in blocks of 32 without a bound (correlation_kernel.cu:43-55), so
+only C % 32 == 0 is defined behaviour for it.  Skipped where the extension was not built."""
 import numpy as np
 import pytest
 import torch
@@ -21,7 +22,7 @@ def _close(got, ref, rel, what):
     assert (err <= rel * (np.abs(ref) + rms)).all(), f"{what}: max err {err.max():.3e}, rms {rms:.3e}"
 
 
-@pytest.mark.parametrize("shape", [(2, 9, 13, 5, 7, 24, 3), (1, 20, 28, 20, 28, 64, 4), (2, 16, 24, 8, 12, 256, 4)])
+@pytest.mark.parametrize("shape", [(2, 9, 13, 5, 7, 32, 3), (1, 20, 28, 20, 28, 64, 4), (2, 16, 24, 8, 12, 256, 4)])
 def test_forward_and_backward_match_the_reference_extension(shape):
     if not torch.cuda.is_available():
         pytest.fail("GPU test selected but no CUDA device is visible")
