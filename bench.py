@@ -96,7 +96,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(self.index)],
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "20", "-i", str(self.index)],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
@@ -239,11 +239,17 @@ def main():
         torch.cuda.synchronize()
 
     with torch.no_grad():
-        for _ in range(args.warmup):
-            step()
-        barrier()
         sampler = ClockSampler(local_rank)
         sampler.start()
+        for _ in range(args.warmup):
+            step()
+        # the timed region is tens of milliseconds: keep the same workload running until nvidia-smi delivers
+        # its first sample, so that the clock record brackets the timed steps under load
+        t_wait = time.perf_counter()
+        while not sampler.lines and time.perf_counter() - t_wait < 3.0:
+            step()
+            torch.cuda.synchronize()
+        n_before = len(sampler.lines)
         recs = []
         e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
         barrier()
@@ -254,7 +260,12 @@ def main():
             recs.append(r)
         e1.record(stream)
         barrier()
+        t_wait = time.perf_counter()
+        while len(sampler.lines) < n_before + 3 and time.perf_counter() - t_wait < 1.0:
+            step()                      # untimed: same load until a few samples past the timed region exist
+            torch.cuda.synchronize()
         clocks = sampler.stop()
+        clocks["window"] = "same workload from before to after the timed steps (20 ms sampling)"
     ms = e0.elapsed_time(e1)
     if dist is not None:
         tms = torch.tensor([ms], device=device)
