@@ -380,3 +380,38 @@ def test_lookup_is_cuda_graph_capturable():
     torch.cuda.synchronize()
     assert torch.equal(out, blk(coords))
     assert not torch.equal(out, ref)
+
+
+# ------------------------------------------------------------------ randomized shapes
+def _random_cases(n, seed):
+    rng = np.random.default_rng(seed)
+    cases = []
+    for _ in range(n):
+        L = int(rng.integers(1, 5))
+        lo = max(2 << (L - 1), 3)                      # every level at least 2 wide (the reference's limit)
+        H, W = int(rng.integers(lo, 72)), int(rng.integers(lo, 90))
+        cases.append((int(rng.integers(1, 4)), int(rng.integers(1, 9)) * 8, H, W, L, int(rng.integers(1, 5)),
+                      ["bf16", "fp32"][int(rng.integers(0, 2))], int(rng.integers(0, 1 << 30))))
+    return cases
+
+
+@pytest.mark.parametrize("case", _random_cases(24, 2026), ids=lambda c: "B%d_D%d_%dx%d_L%d_r%d_%s" % c[:7])
+def test_random_shapes_build_and_lookup_vs_oracle(case):
+    """Seeded random (B, D, H, W, levels, radius, storage): tensor-core build + lookup against the oracle
+    fed the same bf16-rounded features (so only storage rounding and fp32 summation order remain)."""
+    B, D, H, W, L, r, storage, seed = case
+    rng = np.random.default_rng(seed)
+    f1 = rng.standard_normal((B, D, H, W)).astype(np.float32)
+    f2 = rng.standard_normal((B, D, H, W)).astype(np.float32)
+    coords = (O.coords_grid(B, H, W) + rng.normal(0, max(H, W) / 6.0, (B, 2, H, W))).astype(np.float32)
+    coords[:, :, ::2, ::3] = np.round(coords[:, :, ::2, ::3])          # exact integers too
+    blk = R.CorrBlock(t(f1), t(f2), L, r, storage=storage, math="bf16")
+    pyr = O.corr_pyramid(bf16_round(f1).astype(np.float64), bf16_round(f2).astype(np.float64), L)
+    tol = 2.0 ** -8 if storage == "bf16" else 2e-5
+    for l, v in enumerate(blk.corr_pyramid):
+        rel_close(v[:, 0].float().cpu().numpy(), pyr[l], tol, f"{case[:7]} level {l}")
+    got_pyr = [v[:, 0].double().cpu().numpy() for v in blk.corr_pyramid]
+    out = blk(t(coords)).cpu().numpy()
+    # lookup on the stored values, oracle in fp64 (in fp32 the oracle's own x/2^l + offset rounds the
+    # fractional part by up to 4e-6 at |x| ~ 50, which shows up as 1e-5 on steep taps)
+    rel_close(out, O.window_lookup(got_pyr, coords.astype(np.float64), r), 2e-5, f"{case[:7]} lookup")
