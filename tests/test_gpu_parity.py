@@ -415,3 +415,22 @@ def test_random_shapes_build_and_lookup_vs_oracle(case):
     # lookup on the stored values, oracle in fp64 (in fp32 the oracle's own x/2^l + offset rounds the
     # fractional part by up to 4e-6 at |x| ~ 50, which shows up as 1e-5 on steep taps)
     rel_close(out, O.window_lookup(got_pyr, coords.astype(np.float64), r), 2e-5, f"{case[:7]} lookup")
+
+
+def test_video_shape_beyond_32bit_offsets():
+    """BASELINE config 4's shape (1080x1920 -> 135x240 features), two pairs: the bf16 pyramid has 2.9 G
+    elements (> 2^31), so every slab offset must be 64-bit.  Checker: this library's on-the-fly block
+    (fp32, pinned to the reference extension in test_gpu_ref_extension.py), which never forms the volume."""
+    B, D, H, W = 2, 64, 135, 240
+    g = torch.Generator(device="cpu").manual_seed(5)
+    f1 = torch.randn(B, D, H, W, generator=g).to(dev())
+    f2 = torch.randn(B, D, H, W, generator=g).to(dev())
+    c = R.coords_grid(B, H, W, dev()) + 8 * torch.randn(B, 2, H, W, generator=g).to(dev())
+    blk = R.CorrBlock(f1, f2, 4, 4)
+    assert blk.layout.total_elems > 2 ** 31
+    got = blk(c)
+    ref = R.AlternateCorrBlock(f1, f2, 4, 4)(c)
+    rel_close(got.cpu().numpy(), ref.cpu().numpy(), 1e-2, "1080p, bf16 volume vs on-the-fly fp32",
+              floor=bf16_floor(f1.cpu().numpy(), f2.cpu().numpy()))
+    # the last query of the last pair sits at the far end of every level
+    assert torch.isfinite(got[-1, :, -1, -1]).all() and got[-1, :, -1, -1].abs().sum() > 0

@@ -44,6 +44,30 @@ def main():
         ms, up = timeit(cls, 5)
         epe = torch.sqrt(((up - up_ref) ** 2).sum(1)).mean().item()
         res[name] = {"ms": ms, "pairs_per_s": 1e3 * B / ms, "mean_epe_delta_px": epe}
+    # the whole forward (encoders, volume build, 12 x (lookup + update block), upsampling) captured once in a
+    # CUDA graph and replayed: SURVEY 8(f) row 2 -- every call of this library is capturable (no allocation in
+    # the C ABI, no synchronisation, launches on the capturing stream)
+    try:
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            for _ in range(3):
+                Hn.raft_forward(nets, im1, im2, 12, R.CorrBlock)
+        torch.cuda.current_stream().wait_stream(s)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            low_g, up_g = Hn.raft_forward(nets, im1, im2, 12, R.CorrBlock)
+        graph.replay(); torch.cuda.synchronize()
+        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(10):
+            graph.replay()
+        e1.record(); torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / 10
+        epe = torch.sqrt(((up_g - up_ref) ** 2).sum(1)).mean().item()
+        res["ours_bf16_cuda_graph"] = {"ms": ms, "pairs_per_s": 1e3 * B / ms, "mean_epe_delta_px": epe}
+    except Exception as e:   # a diagnostic, not a requirement
+        res["ours_bf16_cuda_graph"] = {"error": f"{type(e).__name__}: {str(e)[:200]}"}
     res["mean_flow_px"] = up_ref.norm(dim=1).mean().item()
     print(json.dumps(res))
 
