@@ -1,0 +1,337 @@
+// On-the-fly correlation on the tensor cores ("alternate" path, bf16 operands).
+//
+// Same contract as AlternateCorrBlock.__call__ (core/corr.py:74-91 calling
+// alt_cuda_corr/correlation_kernel.cu:18-119 once per level): the N x N volume is never
+// materialised, every iteration recomputes the dot products its windows need.  The reference and
+// alt.cu do that tap by tap on the CUDA cores (100 dot products of length D per query and level).
+// Here a CTA takes a spatial block of 8 x 16 queries and ONE pyramid level, forms the bounding box
+// of the block's 128 windows in that level, and computes the block's LOCAL volume
+//     C[128 queries, box targets] = f1[128, D] . f2_l[box, D]^T
+// with tcgen05 (bf16 operands, fp32 accumulators in TMEM), 32 x 8 targets (one 128 x 256 UMMA tile)
+// at a time.  Neighbouring queries' windows overlap almost entirely when the flow is smooth, so the
+// box is little larger than one window (25 x 17 targets at level 0 for a constant flow) and the
+// tensor cores do a few times the reference's arithmetic at two orders of magnitude its speed;
+// a box of any size is walked chunk by chunk, so the result is the same for arbitrary coordinates,
+// only slower.  Both operands come in through TMA boxes of the NHWC feature maps; coordinates
+// outside a map arrive as zeros, which IS grid_sample's zeros padding.
+//
+// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = MMA issuer + TMEM owner, warps 2..5 =
+// epilogue (thread = query = TMEM lane).  Per chunk the epilogue reads the accumulator one target
+// row (32 columns) at a time, bounces it through a per-warp shared-memory scratch and lets every
+// lane pick the <= (2r+2) taps of its own window row; the windows collect in shared memory and are
+// interpolated once all chunks are done.  Two TMEM accumulators alternate, so the MMAs of chunk c+1
+// run while chunk c is picked apart.
+#include "common.cuh"
+#include "tc_ptx.cuh"
+
+namespace rc {
+namespace {
+
+using namespace tc;
+
+constexpr int QB_H = 8, QB_W = 16;          // query block (128 queries = UMMA M)
+constexpr int CH_W = 32, CH_H = 8;          // target chunk (256 targets = UMMA N)
+constexpr int KB = 64;                      // bf16 channels per k-block (128 bytes)
+constexpr int A_BYTES = 128 * 128;          // 16 KB
+constexpr int B_BYTES = 256 * 128;          // 32 KB
+constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+constexpr int NSTAGE = 2;
+constexpr int SCR_STRIDE = 36;              // floats per lane in the bounce scratch (16-byte aligned rows)
+constexpr int ATC_THREADS = 192;
+
+struct AtcParams {
+  int B, D, H, W, num_levels, nbx, nby;
+  int Hl[RC_MAX_LEVELS], Wl[RC_MAX_LEVELS];
+  float out_scale;
+};
+
+struct AtcMaps {
+  CUtensorMap f1;                     // fmap1 NHWC bf16: (D, W, H, B), box (64, 16, 8, 1)
+  CUtensorMap f2[RC_MAX_LEVELS];      // fmap2 level l NHWC bf16: (D, W_l, H_l, B), box (64, 32, 8, 1)
+};
+
+// dyn smem: [stages][A 16K | B 32K] (1024-aligned) | scratch 4 x 32 x 36 floats | windows 128 x (T*T+1) floats | barriers
+template <int R>
+__global__ void __launch_bounds__(ATC_THREADS, 1)
+alt_tc_fwd_kernel(const __grid_constant__ AtcMaps maps, const float *__restrict__ coords, float *__restrict__ out,
+                  const AtcParams p) {
+  constexpr int NW = 2 * R + 1, T = 2 * R + 2, WS = T * T + 1;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  const uint32_t sStage = smem_u32(smem);
+  float *scratch = (float *)(smem + NSTAGE * STAGE_BYTES);
+  float *wins = scratch + 4 * 32 * SCR_STRIDE;
+  uint8_t *tail = (uint8_t *)(wins + 128 * WS);
+  tail = (uint8_t *)(((uintptr_t)tail + 15) & ~(uintptr_t)15);
+  const uint32_t sBar = smem_u32(tail);
+  const uint32_t bar_full = sBar, bar_empty = sBar + 8 * NSTAGE;            // [NSTAGE] each
+  const uint32_t bar_t_full = sBar + 16 * NSTAGE, bar_t_empty = bar_t_full + 16;   // [2] each
+  uint32_t *tmem_slot = (uint32_t *)(tail + 16 * NSTAGE + 32);
+  int *bbox = (int *)(tail + 16 * NSTAGE + 48);                             // x0, y0 (min), x1, y1 (max)
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int l = blockIdx.y, b = blockIdx.z;
+  const int qy0 = (blockIdx.x / p.nbx) * QB_H, qx0 = (blockIdx.x % p.nbx) * QB_W;
+  const int Hl = p.Hl[l], Wl = p.Wl[l];
+  const int N1 = p.H * p.W;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < NSTAGE; ++s) {
+      mbar_init(bar_full + 8 * s, 1);
+      mbar_init(bar_empty + 8 * s, 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(bar_t_full + 8 * s, 1);
+      mbar_init(bar_t_empty + 8 * s, 4);
+    }
+    bbox[0] = 1 << 30; bbox[1] = 1 << 30; bbox[2] = -(1 << 30); bbox[3] = -(1 << 30);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(tmem_slot)));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  __syncthreads();
+
+  // ---- every epilogue thread: its query, its window at this level, its share of the bounding box
+  int x0 = 0, y0 = 0, q = -1;
+  float ax = 0.f, ay = 0.f;
+  bool relevant = false;
+  if (warp >= 2) {
+    const int ql = (warp & 3) * 32 + lane;               // TMEM lane = row of the A box = qy * 16 + qx
+    const int yq = qy0 + ql / QB_W, xq = qx0 + ql % QB_W;
+    float *w = wins + ql * WS;
+#pragma unroll 4
+    for (int k = 0; k < T * T; ++k) w[k] = 0.f;
+    if (yq < p.H && xq < p.W) {
+      q = yq * p.W + xq;
+      const float inv = __int_as_float((127 - l) << 23);
+      const float cx = __ldg(coords + ((size_t)b * 2 + 0) * N1 + q) * inv;
+      const float cy = __ldg(coords + ((size_t)b * 2 + 1) * N1 + q) * inv;
+      if (fabsf(cx) < 1.0e7f && fabsf(cy) < 1.0e7f) {
+        const float fx = floorf(cx), fy = floorf(cy);
+        x0 = (int)fx - R; y0 = (int)fy - R;
+        ax = cx - fx; ay = cy - fy;
+        relevant = x0 + T > 0 && x0 < Wl && y0 + T > 0 && y0 < Hl;     // the window meets the map
+      }
+    }
+    if (relevant) {
+      atomicMin(&bbox[0], max(x0, 0));
+      atomicMin(&bbox[1], max(y0, 0));
+      atomicMax(&bbox[2], min(x0 + T - 1, Wl - 1));
+      atomicMax(&bbox[3], min(y0 + T - 1, Hl - 1));
+    }
+  }
+  fence_before();
+  __syncthreads();
+  fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int bx0 = bbox[0], by0 = bbox[1];
+  const int nx = bbox[2] >= bx0 ? (bbox[2] - bx0) / CH_W + 1 : 0;
+  const int ny = bbox[3] >= by0 ? (bbox[3] - by0) / CH_H + 1 : 0;
+  const int nchunks = nx * ny;
+  const int NKB = p.D / KB;
+
+  if (warp == 0) {
+    // ===================================================== TMA producer
+    if (lane == 0) {
+      uint32_t st = 0, ph = 0;
+      for (int c = 0; c < nchunks; ++c) {
+        const int cx0 = bx0 + (c % nx) * CH_W, cy0 = by0 + (c / nx) * CH_H;
+        for (int kb = 0; kb < NKB; ++kb) {
+          mbar_wait(bar_empty + 8 * st, ph ^ 1);
+          mbar_expect_tx(bar_full + 8 * st, STAGE_BYTES);
+          const uint32_t dst = sStage + st * STAGE_BYTES;
+          tma_load_4d(dst, &maps.f1, bar_full + 8 * st, kb * KB, qx0, qy0, b);
+          tma_load_4d(dst + A_BYTES, &maps.f2[l], bar_full + 8 * st, kb * KB, cx0, cy0, b);
+          if (++st == NSTAGE) { st = 0; ph ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================================== MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t IDESC = idesc_bf16(128, 256);
+      uint32_t st = 0, ph = 0;
+      for (int c = 0; c < nchunks; ++c) {
+        const uint32_t acc = c & 1;
+        mbar_wait(bar_t_empty + 8 * acc, ((c >> 1) & 1) ^ 1);
+        fence_after();
+        for (int kb = 0; kb < NKB; ++kb) {
+          mbar_wait(bar_full + 8 * st, ph);
+          fence_after();
+          const uint32_t al = desc_lo(sStage + st * STAGE_BYTES), bl = desc_lo(sStage + st * STAGE_BYTES + A_BYTES);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            umma_bf16(tmem_base + acc * 256, desc_make(al + 2 * k), desc_make(bl + 2 * k), IDESC, (kb | k) != 0);
+          umma_commit(bar_empty + 8 * st);
+          if (++st == NSTAGE) { st = 0; ph ^= 1; }
+        }
+        umma_commit(bar_t_full + 8 * acc);
+      }
+    }
+  } else {
+    // ===================================================== epilogue: pick the window taps out of every chunk
+    const int quarter = warp & 3;
+    const int ql = quarter * 32 + lane;
+    float *w = wins + ql * WS;
+    float *scr = scratch + (quarter * 32 + lane) * SCR_STRIDE;
+    for (int c = 0; c < nchunks; ++c) {
+      const uint32_t acc = c & 1;
+      const int cx0 = bx0 + (c % nx) * CH_W, cy0 = by0 + (c / nx) * CH_H;
+      mbar_wait(bar_t_full + 8 * acc, (c >> 1) & 1);
+      fence_after();
+      const uint32_t taddr = tmem_base + acc * 256 + ((uint32_t)(quarter * 32) << 16);
+      const int i_lo = max(cx0 - x0, 0), i_hi = min(cx0 + CH_W - x0, T);     // window columns inside this chunk
+#pragma unroll 1
+      for (int rr = 0; rr < CH_H; ++rr) {
+        const int j = cy0 + rr - y0;                                         // window row of this target row
+        const bool need = relevant && j >= 0 && j < T && i_lo < i_hi;
+        if (!__any_sync(0xffffffffu, need)) continue;
+        uint32_t v[32];
+        tmem_ld32(taddr + rr * CH_W, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          *reinterpret_cast<uint4 *>(scr + 4 * k) = make_uint4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+        __syncwarp();
+        if (need) {
+          for (int i = i_lo; i < i_hi; ++i) w[j * T + i] = scr[x0 + i - cx0];
+        }
+        __syncwarp();
+      }
+      fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_t_empty + 8 * acc);
+    }
+
+    // ---- bilinear interpolation of the finished window; channel = l*NW*NW + i*NW + j (x slow, y fast)
+    if (q >= 0) {
+      const int C = p.num_levels * NW * NW;
+      float *op = out + ((size_t)b * C + (size_t)l * NW * NW) * N1 + q;
+      float hprev[NW];
+#pragma unroll
+      for (int j = 0; j < T; ++j) {
+        float h[NW];
+#pragma unroll
+        for (int i = 0; i < NW; ++i) {
+          const float v0 = w[j * T + i], v1 = w[j * T + i + 1];
+          h[i] = fmaf(ax, v1 - v0, v0);
+        }
+        if (j > 0) {
+#pragma unroll
+          for (int i = 0; i < NW; ++i)
+            op[(size_t)(i * NW + (j - 1)) * N1] = fmaf(ay, h[i] - hprev[i], hprev[i]) * p.out_scale;
+        }
+#pragma unroll
+        for (int i = 0; i < NW; ++i) hprev[i] = h[i];
+      }
+    }
+  }
+
+  fence_before();
+  __syncthreads();
+  fence_after();
+  if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base));
+}
+
+}  // namespace
+
+namespace {
+
+__global__ void __launch_bounds__(256)
+f32_to_bf16_kernel(const float *__restrict__ src, __nv_bfloat16 *__restrict__ dst, long long n4) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+    const float4 v = __ldg(reinterpret_cast<const float4 *>(src) + i);
+    __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+    reinterpret_cast<uint2 *>(dst)[i] = make_uint2(*reinterpret_cast<uint32_t *>(&lo), *reinterpret_cast<uint32_t *>(&hi));
+  }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = [] {
+    void *ptr = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) != cudaSuccess ||
+        qres != cudaDriverEntryPointSuccess)
+      ptr = nullptr;
+    return (EncodeTiledFn)ptr;
+  }();
+  return fn;
+}
+
+// NHWC bf16 feature map as a 4-D tensor (D, W, H, B) with a (64, bw, bh, 1) box, 128-byte swizzle
+int encode_nhwc(CUtensorMap *map, const void *base, int B, int D, int H, int W, int bw, int bh) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) {
+    set_error("cuTensorMapEncodeTiled is not available from the CUDA driver");
+    return RC_ECUDA;
+  }
+  cuuint64_t dims[4] = {(cuuint64_t)D, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
+  cuuint64_t str[3] = {(cuuint64_t)D * 2, (cuuint64_t)W * D * 2, (cuuint64_t)H * W * D * 2};
+  cuuint32_t box[4] = {(cuuint32_t)KB, (cuuint32_t)bw, (cuuint32_t)bh, 1};
+  cuuint32_t ones[4] = {1, 1, 1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void *>(base), dims, str, box, ones,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled(feature map %dx%dx%d) failed with CUresult %d", H, W, D, (int)r);
+    return RC_ECUDA;
+  }
+  return RC_OK;
+}
+
+template <int R>
+int alt_tc_launch(const AtcMaps &maps, const float *coords, float *out, const AtcParams &p, cudaStream_t s) {
+  constexpr int T = 2 * R + 2;
+  const size_t smem = 1024 + (size_t)NSTAGE * STAGE_BYTES + 4 * 32 * SCR_STRIDE * sizeof(float) +
+                      128 * (T * T + 1) * sizeof(float) + 256;
+  auto kern = alt_tc_fwd_kernel<R>;
+  RC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  dim3 grid(p.nbx * p.nby, p.num_levels, p.B);
+  kern<<<grid, ATC_THREADS, smem, s>>>(maps, coords, out, p);
+  RC_LAUNCH_CHECK("alt_tc_fwd_kernel");
+  return RC_OK;
+}
+
+}  // namespace
+
+int launch_alt_features_bf16(const float *src, void *dst, long long elems, cudaStream_t s) {
+  const long long n4 = elems / 4;
+  if (n4 == 0) return RC_OK;
+  const int blocks = (int)((n4 + 255) / 256 < 148LL * 8 ? (n4 + 255) / 256 : 148LL * 8);
+  f32_to_bf16_kernel<<<blocks, 256, 0, s>>>(src, (__nv_bfloat16 *)dst, n4);
+  RC_LAUNCH_CHECK("f32_to_bf16_kernel");
+  return RC_OK;
+}
+
+int launch_alt_lookup_tc(const void *f1_bf16, const void *f2_pyr_bf16, const float *coords, int B, int D, int H,
+                         int W, int num_levels, int radius, const int64_t *off, float *out, cudaStream_t s) {
+  AtcParams p{};
+  p.B = B; p.D = D; p.H = H; p.W = W; p.num_levels = num_levels;
+  p.nbx = ceil_div(W, QB_W); p.nby = ceil_div(H, QB_H);
+  p.out_scale = 1.0f / sqrtf((float)D);
+  AtcMaps maps;
+  int r = encode_nhwc(&maps.f1, f1_bf16, B, D, H, W, QB_W, QB_H);
+  if (r) return r;
+  for (int l = 0; l < RC_MAX_LEVELS; ++l) {
+    const int ll = l < num_levels ? l : 0;
+    p.Hl[l] = H >> ll; p.Wl[l] = W >> ll;
+    r = encode_nhwc(&maps.f2[l], (const __nv_bfloat16 *)f2_pyr_bf16 + off[ll], B, D, H >> ll, W >> ll, CH_W, CH_H);
+    if (r) return r;
+  }
+  switch (radius) {
+    case 1: return alt_tc_launch<1>(maps, coords, out, p, s);
+    case 2: return alt_tc_launch<2>(maps, coords, out, p, s);
+    case 3: return alt_tc_launch<3>(maps, coords, out, p, s);
+    case 4: return alt_tc_launch<4>(maps, coords, out, p, s);
+    default: set_error("radius %d unsupported (1..4)", radius); return RC_EINVAL;
+  }
+}
+
+}  // namespace rc

@@ -29,6 +29,10 @@ int launch_alt_bwd(const float *fmap1, const float *fmap2, const float *coords, 
                    float *g2, cudaStream_t s);
 int launch_alt_pool(const float *fmap1, const float *fmap2, int B, int D, int H, int W, int num_levels,
                     const int64_t *off, float *f1_nhwc, float *f2_pyr, cudaStream_t s);
+// alt_tc.cu
+int launch_alt_features_bf16(const float *src, void *dst, long long elems, cudaStream_t s);
+int launch_alt_lookup_tc(const void *f1_bf16, const void *f2_pyr_bf16, const float *coords, int B, int D, int H,
+                         int W, int num_levels, int radius, const int64_t *off, float *out, cudaStream_t s);
 // build_bwd.cu
 int64_t build_bwd_workspace_bytes(int B, int D, int H, int W, int num_levels);
 int launch_build_bwd(const float *grad_pyramid, const float *fmap1, const float *fmap2, int B, int D,
@@ -268,6 +272,32 @@ int rc_alt_lookup_fwd(const float *fmap1_nhwc, const float *fmap2_pyr, const flo
   RC_REQUIRE((H >> (num_levels - 1)) >= 1 && (W >> (num_levels - 1)) >= 1, "map too small for %d levels", num_levels);
   return launch_alt_lookup_fwd(fmap1_nhwc, fmap2_pyr, coords, B, D, H, W, num_levels, radius, off, out,
                                (cudaStream_t)stream);
+}
+
+int rc_alt_features_bf16(const float *fmap1_nhwc, const float *fmap2_pyr, int B, int D, int H, int W,
+                         int num_levels, void *fmap1_bf16, void *fmap2_pyr_bf16, rc_stream_t stream) {
+  RC_REQUIRE(fmap1_nhwc && fmap2_pyr && fmap1_bf16 && fmap2_pyr_bf16, "rc_alt_features_bf16: NULL pointer");
+  RC_REQUIRE(D >= 4 && D % 4 == 0, "rc_alt_features_bf16: D=%d must be a multiple of 4", D);
+  int64_t off[RC_MAX_LEVELS];
+  const int64_t total = rc_alt_feature_pyramid_elems(B, D, H, W, num_levels, off);
+  RC_REQUIRE(total > 0, "rc_alt_features_bf16: bad sizes");
+  int r = launch_alt_features_bf16(fmap1_nhwc, fmap1_bf16, (long long)B * H * W * D, (cudaStream_t)stream);
+  if (r) return r;
+  return launch_alt_features_bf16(fmap2_pyr, fmap2_pyr_bf16, (long long)total, (cudaStream_t)stream);
+}
+
+int rc_alt_lookup_fwd_tc(const void *fmap1_bf16, const void *fmap2_pyr_bf16, const float *coords, int B, int D,
+                         int H, int W, int num_levels, int radius, float *out, rc_stream_t stream) {
+  RC_REQUIRE(fmap1_bf16 && fmap2_pyr_bf16 && coords && out, "rc_alt_lookup_fwd_tc: NULL pointer");
+  RC_REQUIRE(D >= 64 && D % 64 == 0, "rc_alt_lookup_fwd_tc: D=%d must be a multiple of 64", D);
+  RC_REQUIRE(radius >= 1 && radius <= 4, "radius %d unsupported (1..4)", radius);
+  RC_REQUIRE(((uintptr_t)fmap1_bf16 & 127) == 0 && ((uintptr_t)fmap2_pyr_bf16 & 127) == 0,
+             "rc_alt_lookup_fwd_tc: feature buffers must be 128-byte aligned");
+  int64_t off[RC_MAX_LEVELS];
+  RC_REQUIRE(rc_alt_feature_pyramid_elems(B, D, H, W, num_levels, off) > 0, "rc_alt_lookup_fwd_tc: bad sizes");
+  RC_REQUIRE((H >> (num_levels - 1)) >= 1 && (W >> (num_levels - 1)) >= 1, "map too small for %d levels", num_levels);
+  return launch_alt_lookup_tc(fmap1_bf16, fmap2_pyr_bf16, coords, B, D, H, W, num_levels, radius, off, out,
+                              (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -434,3 +434,40 @@ def test_video_shape_beyond_32bit_offsets():
               floor=bf16_floor(f1.cpu().numpy(), f2.cpu().numpy()))
     # the last query of the last pair sits at the far end of every level
     assert torch.isfinite(got[-1, :, -1, -1]).all() and got[-1, :, -1, -1].abs().sum() > 0
+
+
+# ------------------------------------------------------------------ on-the-fly path on the tensor cores
+@pytest.mark.parametrize("kind", ["smooth", "rand", "int", "far", "edge"])
+@pytest.mark.parametrize("shape", [(1, 64, 24, 40, 4), (2, 128, 19, 45, 3), (1, 256, 55, 128, 4)])
+def test_alternate_tensor_core_matches_fp32_path(shape, kind):
+    """rc_alt_lookup_fwd_tc against rc_alt_lookup_fwd (fp32, itself pinned to the reference extension) fed
+    bf16-rounded features: what remains is fp32 summation order.  Coordinates: a smooth flow (small
+    boxes), random (boxes of many chunks), exact integers, far outside (all zeros), straddling the border."""
+    B, D, H, W, r = shape
+    rng = np.random.default_rng(H * W + D + len(kind))
+    f1 = bf16_round(rng.standard_normal((B, D, H, W)).astype(np.float32))
+    f2 = bf16_round(rng.standard_normal((B, D, H, W)).astype(np.float32))
+    grid = O.coords_grid(B, H, W)
+    if kind == "smooth":
+        yy, xx = np.meshgrid(np.arange(H), np.arange(W), indexing="ij")
+        flow = np.stack([3.3 + 0.05 * xx + 0.02 * yy, -2.7 + 0.03 * yy - 0.01 * xx])[None]
+        coords = grid + flow
+    elif kind == "rand":
+        coords = grid + rng.normal(0, 6, (B, 2, H, W))
+    elif kind == "int":
+        coords = grid + np.round(rng.normal(0, 3, (B, 2, 1, 1)))
+    elif kind == "far":
+        coords = grid + 1.0e4
+    else:
+        coords = grid + np.array([W - 6.5, -(H - 5.25)]).reshape(1, 2, 1, 1) * (grid[:, :1] > W / 2)
+    coords = coords.astype(np.float32)
+    ref = R.AlternateCorrBlock(t(f1), t(f2), 4, r)(t(coords))
+    got = R.AlternateCorrBlock(t(f1), t(f2), 4, r, math="bf16")(t(coords))
+    assert got.shape == ref.shape
+    n = (2 * r + 1) ** 2
+    # level 0 sees the same bf16 features in both paths: only fp32 summation order differs
+    rel_close(got[:, :n].cpu().numpy(), ref[:, :n].cpu().numpy(), 2e-5, f"alt tensor-core {shape} {kind} level 0")
+    # levels 1..3: the pooled features are rounded to bf16 only on the tensor-core path: 1e-2 (bf16)
+    rel_close(got.cpu().numpy(), ref.cpu().numpy(), 1e-2, f"alt tensor-core {shape} {kind}", floor=bf16_floor(f1, f2))
+    if kind == "far":
+        assert not got.any().item()

@@ -60,8 +60,18 @@ with torch.no_grad():
         coords = R.coords_grid(1, H, W, dev) + 5 * torch.randn(1, 2, H, W, generator=g).to(dev)
         ref = ref_block(f1, f2)
         ours = R.AlternateCorrBlock(f1, f2, 4, 4)
+        ours_tc = R.AlternateCorrBlock(f1, f2, 4, 4, math="bf16")
         ms_ref, o_ref = timeit(lambda: ref(coords), 5)
         ms_ours, o_ours = timeit(lambda: ours(coords), 10)
         err = ((o_ours - o_ref).abs().max() / o_ref.abs().max()).item()
         res[name] = {"reference_ext_ms": ms_ref, "ours_ms": ms_ours, "speedup": ms_ref / ms_ours, "max_rel_diff": err}
+        # tensor-core variant: a smooth flow (what video gives) and the scattered random one
+        ys, xs = torch.meshgrid(torch.arange(H, device=dev), torch.arange(W, device=dev), indexing="ij")
+        smooth = R.coords_grid(1, H, W, dev) + torch.stack([3.3 + 0.02 * xs, -2.7 + 0.03 * ys])[None].float()
+        for tag, cc in (("smooth_flow", smooth), ("random_flow_sigma5", coords)):
+            ms_tc, o_tc = timeit(lambda: ours_tc(cc), 20)
+            ms_f, o_f = timeit(lambda: ours(cc), 10)
+            res[name][f"ours_tc_ms_{tag}"] = ms_tc
+            res[name][f"ours_fp32_ms_{tag}"] = ms_f
+            res[name][f"tc_vs_fp32_max_rel_diff_{tag}"] = ((o_tc - o_f).abs().max() / o_f.abs().max()).item()
 print(json.dumps(res))
