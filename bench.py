@@ -401,6 +401,8 @@ def run_extras(R, device, args, pk):
             out["b1_build_fp32_simt_ms"] = timeit(lambda: R.CorrBlock(f1, f2, LEVELS, RADIUS, storage="fp32", math="fp32"), 3)
             alt = R.AlternateCorrBlock(f1, f2, LEVELS, RADIUS)
             out["b1_alt_lookup_ms"] = timeit(lambda: alt(coords[0]), 10)
+            alt_tc = R.AlternateCorrBlock(f1, f2, LEVELS, RADIUS, math="bf16")
+            out["b1_alt_tc_lookup_ms"] = timeit(lambda: alt_tc(coords[0]), 30)
         # training direction at the FlyingChairs shape (config 5): 46x62, batch 10
         g = torch.Generator(device="cpu").manual_seed(3)
         Bc, Hc, Wc = 10, 46, 62
@@ -438,6 +440,8 @@ def run_extras(R, device, args, pk):
             del blk
             altv = R.AlternateCorrBlock(v1, v2, LEVELS, RADIUS)
             out["v1080_alt_lookup_ms"] = timeit(lambda: altv(cv), 5)
+            altv_tc = R.AlternateCorrBlock(v1, v2, LEVELS, RADIUS, math="bf16")
+            out["v1080_alt_tc_lookup_ms"] = timeit(lambda: altv_tc(cv), 20)
             out["v1080_note"] = "12 iterations: default = build + 12 lookups; on-the-fly = 12 alt lookups (no volume in memory)"
     except Exception as e:  # extras must never sink the headline
         out["error"] = f"{type(e).__name__}: {e}"

@@ -35,7 +35,7 @@ constexpr int KB = 64;                      // bf16 channels per k-block (128 by
 constexpr int A_BYTES = 128 * 128;          // 16 KB
 constexpr int B_BYTES = 256 * 128;          // 32 KB
 constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-constexpr int NSTAGE = 2;
+constexpr int NSTAGE = 3;
 constexpr int SCR_STRIDE = 36;              // floats per lane in the bounce scratch (16-byte aligned rows)
 constexpr int ATC_THREADS = 192;
 
@@ -196,7 +196,12 @@ alt_tc_fwd_kernel(const __grid_constant__ AtcMaps maps, const float *__restrict_
           *reinterpret_cast<uint4 *>(scr + 4 * k) = make_uint4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
         __syncwarp();
         if (need) {
-          for (int i = i_lo; i < i_hi; ++i) w[j * T + i] = scr[x0 + i - cx0];
+          float tv[T];
+#pragma unroll
+          for (int i = 0; i < T; ++i) tv[i] = scr[min(max(x0 + i - cx0, 0), CH_W - 1)];    // all loads first
+#pragma unroll
+          for (int i = 0; i < T; ++i)
+            if (i >= i_lo && i < i_hi) w[j * T + i] = tv[i];
         }
         __syncwarp();
       }

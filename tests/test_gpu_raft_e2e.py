@@ -59,6 +59,13 @@ def test_flow_with_on_the_fly_correlation(reference_run):
     assert _epe(got, up) <= 1e-3
 
 
+def test_flow_with_on_the_fly_correlation_on_tensor_cores(reference_run):
+    nets, im1, im2, low, up = reference_run
+    _, got = Hn.raft_forward(nets, im1, im2, iters=12, corr_cls=partial(R.AlternateCorrBlock, math="bf16"))
+    d = _epe(got, up)
+    assert d <= 0.01, f"mean EPE delta {d:.5f} px > 0.01 px"
+
+
 class _JitteredReference(Hn.TorchCorrBlock):
     """The reference block with 1e-7 relative noise on its output: the yardstick for how much the rest
     of the network amplifies a last-bit difference in the correlation features."""

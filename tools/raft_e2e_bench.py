@@ -40,7 +40,8 @@ def main():
     res["torch_corrblock_on_gpu"] = {"ms": ms_ref, "pairs_per_s": 1e3 * B / ms_ref}
     for name, cls in (("ours_bf16_tensor_core", R.CorrBlock),
                       ("ours_fp32", partial(R.CorrBlock, storage="fp32", math="fp32")),
-                      ("ours_on_the_fly", R.AlternateCorrBlock)):
+                      ("ours_on_the_fly", R.AlternateCorrBlock),
+                      ("ours_on_the_fly_tensor_core", partial(R.AlternateCorrBlock, math="bf16"))):
         ms, up = timeit(cls, 5)
         epe = torch.sqrt(((up - up_ref) ** 2).sum(1)).mean().item()
         res[name] = {"ms": ms, "pairs_per_s": 1e3 * B / ms, "mean_epe_delta_px": epe}
