@@ -50,6 +50,22 @@ struct AtcMaps {
   CUtensorMap f2[RC_MAX_LEVELS];      // fmap2 level l NHWC bf16: (D, W_l, H_l, B), box (64, 32, 8, 1)
 };
 
+// Window of one query at pyramid level l: origin (x0, y0) of its (2r+2)^2 taps, the bilinear fractions, and
+// whether it meets the map at all (coords / 2^l as core/corr.py:40, taps as correlation_kernel.cu:59-116).
+template <int R>
+__device__ __forceinline__ bool window_at_level(float cxf, float cyf, int l, int Hl, int Wl, int &x0, int &y0,
+                                                float &ax, float &ay) {
+  constexpr int T = 2 * R + 2;
+  const float inv = __int_as_float((127 - l) << 23);
+  const float cx = cxf * inv, cy = cyf * inv;
+  x0 = 0; y0 = 0; ax = 0.f; ay = 0.f;
+  if (!(fabsf(cx) < 1.0e7f && fabsf(cy) < 1.0e7f)) return false;
+  const float fx = floorf(cx), fy = floorf(cy);
+  x0 = (int)fx - R; y0 = (int)fy - R;
+  ax = cx - fx; ay = cy - fy;
+  return x0 + T > 0 && x0 < Wl && y0 + T > 0 && y0 < Hl;
+}
+
 // dyn smem: [stages][A 16K | B 32K] (1024-aligned) | scratch 4 x 32 x 36 floats | windows 128 x (T*T+1) floats | barriers
 template <int R>
 __global__ void __launch_bounds__(ATC_THREADS, 1)
@@ -240,6 +256,312 @@ alt_tc_fwd_kernel(const __grid_constant__ AtcMaps maps, const float *__restrict_
   if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base));
 }
 
+// ------------------------------------------------------------------------------------------------
+// Persistent variant for D <= 256 (every configuration the reference ships).
+//
+// The kernel above reloads the query block's features with every k-block of every chunk, and every
+// CTA pays its own prologue (barrier init, TMEM allocation, coordinates, pipeline fill) for two or
+// three chunks of work: at a full batch it is bound by the L2 -> shared-memory traffic (192 KB per
+// chunk against 2048 tensor-core cycles) and by those bubbles.  Here one CTA per SM walks a list
+// of work units; a unit is one 8 x 16 query block and a run of pyramid levels.  The block's own
+// features (128 x D bf16, up to 64 KB) are loaded ONCE per unit and stay in shared memory while the
+// chunks of all its levels stream through a 3-stage ring, so a chunk costs 128 KB of L2 traffic
+// instead of 192; the producer warp works out the bounding boxes of the coming levels itself and
+// hands them to the other warps through a small descriptor ring, so loads, MMAs and tap picking of
+// consecutive levels and units overlap without a CTA-wide barrier.  The bounce scratch is stored
+// column-major (one bank per lane), which makes the tap picking free of bank conflicts.
+constexpr int P_NSTAGE = 3;
+constexpr int P_MAX_KB = 4;                 // resident query features: up to 4 k-blocks = 256 channels
+constexpr int P_NDESC = 4;
+constexpr int P_TAIL_BYTES = 320;
+
+struct PersistParams {
+  AtcParams a;
+  int n_units, n_items, nsplit, lpu;        // items = B * blocks; units = items * nsplit; lpu = levels per unit
+};
+
+struct LevelDesc { int bx0, by0, nx, ny; };
+
+template <int R>
+__global__ void __launch_bounds__(ATC_THREADS, 1)
+alt_tc_persist_kernel(const __grid_constant__ AtcMaps maps, const float *__restrict__ coords,
+                      float *__restrict__ out, const PersistParams pp) {
+  constexpr int NW = 2 * R + 1, T = 2 * R + 2, WS = T * T + 1;
+  const AtcParams &p = pp.a;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  if ((smem_u32(smem) & 1023u) != 0) __trap();            // the swizzled operand tiles need 1024-byte alignment
+  const uint32_t sA = smem_u32(smem);                                       // P_MAX_KB x 16 KB
+  const uint32_t sB = sA + P_MAX_KB * A_BYTES;                              // P_NSTAGE x 32 KB
+  float *scratch = (float *)(smem + P_MAX_KB * A_BYTES + P_NSTAGE * B_BYTES);   // 4 warps x [32 cols][32 lanes]
+  float *wins = scratch + 4 * 32 * 32;
+  uint8_t *tail = (uint8_t *)(wins + 128 * WS);
+  tail = (uint8_t *)(((uintptr_t)tail + 15) & ~(uintptr_t)15);
+  const uint32_t sBar = smem_u32(tail);
+  const uint32_t b_full = sBar, b_empty = sBar + 8 * P_NSTAGE;              // 3 + 3
+  const uint32_t a_full = sBar + 48, a_empty = a_full + 8 * P_MAX_KB;       // 4 + 4
+  const uint32_t t_full = sBar + 112, t_empty = t_full + 16;                // 2 + 2
+  const uint32_t d_full = sBar + 144, d_empty = d_full + 8 * P_NDESC;       // 4 + 4
+  uint32_t *tmem_slot = (uint32_t *)(tail + 208);
+  LevelDesc *descs = (LevelDesc *)(tail + 224);                             // P_NDESC x 16 B
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int N1 = p.H * p.W;
+  const int NKB = p.D / KB;
+  const int nblk = p.nbx * p.nby;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < P_NSTAGE; ++s) { mbar_init(b_full + 8 * s, 1); mbar_init(b_empty + 8 * s, 1); }
+    for (int s = 0; s < P_MAX_KB; ++s) { mbar_init(a_full + 8 * s, 1); mbar_init(a_empty + 8 * s, 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(t_full + 8 * s, 1); mbar_init(t_empty + 8 * s, 4); }
+    for (int s = 0; s < P_NDESC; ++s) { mbar_init(d_full + 8 * s, 1); mbar_init(d_empty + 8 * s, 5); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(tmem_slot)));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  fence_before();
+  __syncthreads();
+  fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================================================== scout + TMA producer
+    uint32_t st = 0, ph = 0, dcount = 0, nu = 0;
+    for (int u = blockIdx.x; u < pp.n_units; u += gridDim.x, ++nu) {
+      const int lg = u / pp.n_items, item = u - lg * pp.n_items;      // fine levels (most chunks) first
+      const int b = item / nblk, blk = item - b * nblk;
+      const int qy0 = (blk / p.nbx) * QB_H, qx0 = (blk % p.nbx) * QB_W;
+      const int l_begin = lg * pp.lpu, l_end = min(p.num_levels, l_begin + pp.lpu);
+      if (lane == 0) {
+        for (int kb = 0; kb < NKB; ++kb) {
+          mbar_wait(a_empty + 8 * kb, (nu & 1) ^ 1);
+          mbar_expect_tx(a_full + 8 * kb, A_BYTES);
+          tma_load_4d(sA + kb * A_BYTES, &maps.f1, a_full + 8 * kb, kb * KB, qx0, qy0, b);
+        }
+      }
+      // this lane's share of the block: queries 4*lane .. 4*lane+3 (a quarter of one block row)
+      float cxs[4], cys[4];
+      bool inside[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int ql = lane * 4 + k;
+        const int yq = qy0 + ql / QB_W, xq = qx0 + ql % QB_W;
+        inside[k] = yq < p.H && xq < p.W;
+        const int q = inside[k] ? yq * p.W + xq : 0;
+        cxs[k] = __ldg(coords + ((size_t)b * 2 + 0) * N1 + q);
+        cys[k] = __ldg(coords + ((size_t)b * 2 + 1) * N1 + q);
+      }
+      for (int l = l_begin; l < l_end; ++l) {
+        const int Hl = p.Hl[l], Wl = p.Wl[l];
+        int mnx = 1 << 30, mny = 1 << 30, mxx = -(1 << 30), mxy = -(1 << 30);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          int x0, y0;
+          float ax, ay;
+          if (inside[k] && window_at_level<R>(cxs[k], cys[k], l, Hl, Wl, x0, y0, ax, ay)) {
+            mnx = min(mnx, max(x0, 0));
+            mny = min(mny, max(y0, 0));
+            mxx = max(mxx, min(x0 + T - 1, Wl - 1));
+            mxy = max(mxy, min(y0 + T - 1, Hl - 1));
+          }
+        }
+        mnx = __reduce_min_sync(0xffffffffu, mnx);
+        mny = __reduce_min_sync(0xffffffffu, mny);
+        mxx = __reduce_max_sync(0xffffffffu, mxx);
+        mxy = __reduce_max_sync(0xffffffffu, mxy);
+        const int nx = mxx >= mnx ? (mxx - mnx) / CH_W + 1 : 0;
+        const int ny = mxy >= mny ? (mxy - mny) / CH_H + 1 : 0;
+        if (lane == 0) {
+          const uint32_t slot = dcount % P_NDESC;
+          mbar_wait(d_empty + 8 * slot, ((dcount / P_NDESC) & 1) ^ 1);
+          descs[slot] = LevelDesc{mnx, mny, nx, ny};
+          mbar_arrive(d_full + 8 * slot);
+          int cx0 = mnx - CH_W, cy0 = mny, ccol = 0;
+          for (int c = 0; c < nx * ny; ++c) {
+            cx0 += CH_W;
+            if (ccol == nx) { ccol = 0; cx0 = mnx; cy0 += CH_H; }
+            ++ccol;
+            for (int kb = 0; kb < NKB; ++kb) {
+              mbar_wait(b_empty + 8 * st, ph ^ 1);
+              mbar_expect_tx(b_full + 8 * st, B_BYTES);
+              tma_load_4d(sB + st * B_BYTES, &maps.f2[l], b_full + 8 * st, kb * KB, cx0, cy0, b);
+              if (++st == P_NSTAGE) { st = 0; ph ^= 1; }
+            }
+          }
+        }
+        ++dcount;
+        __syncwarp();
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================================== MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t IDESC = idesc_bf16(128, 256);
+      uint32_t st = 0, ph = 0, dcount = 0, nu = 0, g = 0;
+      for (int u = blockIdx.x; u < pp.n_units; u += gridDim.x, ++nu) {
+        const int lg = u / pp.n_items;
+        const int l_begin = lg * pp.lpu, l_end = min(p.num_levels, l_begin + pp.lpu);
+        bool released = false, first = true;
+        for (int l = l_begin; l < l_end; ++l, ++dcount) {
+          const uint32_t slot = dcount % P_NDESC;
+          mbar_wait(d_full + 8 * slot, (dcount / P_NDESC) & 1);
+          const int nchunks = descs[slot].nx * descs[slot].ny;
+          mbar_arrive(d_empty + 8 * slot);
+          for (int c = 0; c < nchunks; ++c, ++g) {
+            const uint32_t acc = g & 1;
+            const bool last = (l == l_end - 1) && (c == nchunks - 1);
+            mbar_wait(t_empty + 8 * acc, ((g >> 1) & 1) ^ 1);
+            fence_after();
+            for (int kb = 0; kb < NKB; ++kb) {
+              if (first) mbar_wait(a_full + 8 * kb, nu & 1);
+              mbar_wait(b_full + 8 * st, ph);
+              fence_after();
+              const uint32_t al = desc_lo(sA + kb * A_BYTES), bl = desc_lo(sB + st * B_BYTES);
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                umma_bf16(tmem_base + acc * 256, desc_make(al + 2 * k), desc_make(bl + 2 * k), IDESC, (kb | k) != 0);
+              umma_commit(b_empty + 8 * st);
+              if (last) umma_commit(a_empty + 8 * kb);      // this resident k-block is free once its MMAs are done
+              if (++st == P_NSTAGE) { st = 0; ph ^= 1; }
+            }
+            umma_commit(t_full + 8 * acc);
+            first = false;
+            released |= last;
+          }
+        }
+        if (!released) {
+          // the last level had no chunk: hand the resident features back here
+          for (int kb = 0; kb < NKB; ++kb) {
+            if (first) mbar_wait(a_full + 8 * kb, nu & 1);
+            umma_commit(a_empty + 8 * kb);
+          }
+        }
+      }
+    }
+  } else {
+    // ===================================================== epilogue: pick the window taps out of every chunk
+    const int quarter = warp & 3;
+    const int ql = quarter * 32 + lane;                    // TMEM lane = row of the A box = qy * 16 + qx
+    float *w = wins + ql * WS;
+    float *scr = scratch + quarter * 32 * 32 + lane;       // column c of this lane's row sits at scr[c * 32]
+    uint32_t dcount = 0, g = 0;
+    // this thread's query in a unit and its coordinates, fetched one unit ahead of their use
+    int q_nx = -1, b_nx = 0;
+    float cx_nx = 0.f, cy_nx = 0.f;
+    auto fetch = [&](int u) {
+      if (u >= pp.n_units) return;
+      const int item = u % pp.n_items;
+      b_nx = item / nblk;
+      const int blk = item - b_nx * nblk;
+      const int yq = (blk / p.nbx) * QB_H + ql / QB_W, xq = (blk % p.nbx) * QB_W + ql % QB_W;
+      q_nx = (yq < p.H && xq < p.W) ? yq * p.W + xq : -1;
+      if (q_nx >= 0) {
+        cx_nx = __ldg(coords + ((size_t)b_nx * 2 + 0) * N1 + q_nx);
+        cy_nx = __ldg(coords + ((size_t)b_nx * 2 + 1) * N1 + q_nx);
+      }
+    };
+    fetch(blockIdx.x);
+    for (int u = blockIdx.x; u < pp.n_units; u += gridDim.x) {
+      const int lg = u / pp.n_items;                                  // fine levels (most chunks) first
+      const int l_begin = lg * pp.lpu, l_end = min(p.num_levels, l_begin + pp.lpu);
+      const int q = q_nx, b = b_nx;
+      const float cxf = cx_nx, cyf = cy_nx;
+      fetch(u + gridDim.x);
+      for (int l = l_begin; l < l_end; ++l, ++dcount) {
+        int x0 = 0, y0 = 0;
+        float ax = 0.f, ay = 0.f;
+        const bool relevant = q >= 0 && window_at_level<R>(cxf, cyf, l, p.Hl[l], p.Wl[l], x0, y0, ax, ay);
+        // every in-map tap of a relevant window lies in some chunk and is overwritten below; only windows that
+        // leave the map (or miss it) keep zeros
+        if (!relevant || x0 < 0 || y0 < 0 || x0 + T > p.Wl[l] || y0 + T > p.Hl[l]) {
+#pragma unroll 4
+          for (int k = 0; k < T * T; ++k) w[k] = 0.f;
+        }
+        const uint32_t slot = dcount % P_NDESC;
+        mbar_wait(d_full + 8 * slot, (dcount / P_NDESC) & 1);
+        const LevelDesc d = descs[slot];
+        __syncwarp();
+        if (lane == 0) mbar_arrive(d_empty + 8 * slot);
+        const int nchunks = d.nx * d.ny;
+        int cx0 = d.bx0 - CH_W, cy0 = d.by0, ccol = 0;
+        for (int c = 0; c < nchunks; ++c, ++g) {
+          const uint32_t acc = g & 1;
+          cx0 += CH_W;
+          if (ccol == d.nx) { ccol = 0; cx0 = d.bx0; cy0 += CH_H; }
+          ++ccol;
+          const int i_lo = max(cx0 - x0, 0), i_hi = min(cx0 + CH_W - x0, T);   // window columns inside this chunk
+          const bool cols = relevant && i_lo < i_hi;
+          // the accumulator columns any lane of this warp wants out of the chunk
+          const int cmin = __reduce_min_sync(0xffffffffu, cols ? x0 + i_lo - cx0 : CH_W);
+          const int cmax = __reduce_max_sync(0xffffffffu, cols ? x0 + i_hi - 1 - cx0 : -1);
+          mbar_wait(t_full + 8 * acc, (g >> 1) & 1);
+          fence_after();
+          const uint32_t taddr = tmem_base + acc * 256 + ((uint32_t)(quarter * 32) << 16);
+#pragma unroll 1
+          for (int rr = 0; rr < CH_H; ++rr) {
+            const int j = cy0 + rr - y0;                                       // window row of this target row
+            const bool need = cols && j >= 0 && j < T;
+            if (!__any_sync(0xffffffffu, need)) continue;
+            uint32_t v[32];
+            tmem_ld32(taddr + rr * CH_W, v);
+            tmem_ld_wait();
+#pragma unroll
+            for (int k8 = 0; k8 < 32; k8 += 8) {
+              if (k8 + 7 >= cmin && k8 <= cmax) {                              // warp-uniform
+#pragma unroll
+                for (int k = k8; k < k8 + 8; ++k) scr[k * 32] = __uint_as_float(v[k]);
+              }
+            }
+            __syncwarp();
+            if (need) {
+              float tv[T];
+#pragma unroll
+              for (int i = 0; i < T; ++i) tv[i] = scr[min(max(x0 + i - cx0, 0), CH_W - 1) * 32];   // all loads first
+#pragma unroll
+              for (int i = 0; i < T; ++i)
+                if (i >= i_lo && i < i_hi) w[j * T + i] = tv[i];
+            }
+            __syncwarp();
+          }
+          fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(t_empty + 8 * acc);
+        }
+
+        // ---- bilinear interpolation of the finished window; channel = l*NW*NW + i*NW + j (x slow, y fast)
+        if (q >= 0) {
+          const int C = p.num_levels * NW * NW;
+          float *op = out + ((size_t)b * C + (size_t)l * NW * NW) * N1 + q;
+          float hprev[NW];
+#pragma unroll
+          for (int j = 0; j < T; ++j) {
+            float h[NW];
+#pragma unroll
+            for (int i = 0; i < NW; ++i) {
+              const float v0 = w[j * T + i], v1 = w[j * T + i + 1];
+              h[i] = fmaf(ax, v1 - v0, v0);
+            }
+            if (j > 0) {
+#pragma unroll
+              for (int i = 0; i < NW; ++i)
+                op[(size_t)(i * NW + (j - 1)) * N1] = fmaf(ay, h[i] - hprev[i], hprev[i]) * p.out_scale;
+            }
+#pragma unroll
+            for (int i = 0; i < NW; ++i) hprev[i] = h[i];
+          }
+        }
+        __syncwarp();
+      }
+    }
+  }
+
+  fence_before();
+  __syncthreads();
+  fence_after();
+  if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base));
+}
+
 }  // namespace
 
 namespace {
@@ -304,6 +626,49 @@ int alt_tc_launch(const AtcMaps &maps, const float *coords, float *out, const At
   return RC_OK;
 }
 
+// Work split of the persistent kernel: a unit is a query block with num_levels / nsplit levels.  One unit per
+// block keeps the block's features resident longest; small batches are cut finer so that every SM has work.
+template <int R>
+int alt_tc_launch_persistent(const AtcMaps &maps, const float *coords, float *out, const AtcParams &p,
+                             cudaStream_t s) {
+  constexpr int T = 2 * R + 2;
+  int dev = 0, sms = 0;
+  RC_CUDA(cudaGetDevice(&dev));
+  RC_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const long long items = (long long)p.B * p.nbx * p.nby;
+  PersistParams pp{};
+  pp.a = p;
+  double best = 0.0;
+  for (int ns = 1; ns <= p.num_levels; ns *= 2) {
+    const int lpu = ceil_div(p.num_levels, ns);
+    const long long units = items * ns;
+    const double cost = (double)((units + sms - 1) / sms) * (2.25 * lpu + 0.5);   // chunks + feature load
+    if (ns == 1 || cost < best) { best = cost; pp.nsplit = ns; pp.lpu = lpu; }
+  }
+  const long long units = items * pp.nsplit;
+  if (units > 0x7fffffffLL) {
+    set_error("alt lookup: %lld work units exceed the 32-bit range", units);
+    return RC_EINVAL;
+  }
+  pp.n_units = (int)units;
+  pp.n_items = (int)items;
+  const size_t smem = (size_t)P_MAX_KB * A_BYTES + (size_t)P_NSTAGE * B_BYTES + 4 * 32 * 32 * sizeof(float) +
+                      128 * (T * T + 1) * sizeof(float) + P_TAIL_BYTES;
+  auto kern = alt_tc_persist_kernel<R>;
+  RC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int grid = (int)(units < sms ? units : sms);
+  if (grid == 0) return RC_OK;
+  kern<<<grid, ATC_THREADS, smem, s>>>(maps, coords, out, pp);
+  RC_LAUNCH_CHECK("alt_tc_persist_kernel");
+  return RC_OK;
+}
+
+template <int R>
+int alt_tc_dispatch(const AtcMaps &maps, const float *coords, float *out, const AtcParams &p, cudaStream_t s) {
+  if (p.D <= P_MAX_KB * KB) return alt_tc_launch_persistent<R>(maps, coords, out, p, s);
+  return alt_tc_launch<R>(maps, coords, out, p, s);
+}
+
 }  // namespace
 
 int launch_alt_features_bf16(const float *src, void *dst, long long elems, cudaStream_t s) {
@@ -331,10 +696,10 @@ int launch_alt_lookup_tc(const void *f1_bf16, const void *f2_pyr_bf16, const flo
     if (r) return r;
   }
   switch (radius) {
-    case 1: return alt_tc_launch<1>(maps, coords, out, p, s);
-    case 2: return alt_tc_launch<2>(maps, coords, out, p, s);
-    case 3: return alt_tc_launch<3>(maps, coords, out, p, s);
-    case 4: return alt_tc_launch<4>(maps, coords, out, p, s);
+    case 1: return alt_tc_dispatch<1>(maps, coords, out, p, s);
+    case 2: return alt_tc_dispatch<2>(maps, coords, out, p, s);
+    case 3: return alt_tc_dispatch<3>(maps, coords, out, p, s);
+    case 4: return alt_tc_dispatch<4>(maps, coords, out, p, s);
     default: set_error("radius %d unsupported (1..4)", radius); return RC_EINVAL;
   }
 }

@@ -438,7 +438,11 @@ def test_video_shape_beyond_32bit_offsets():
 
 # ------------------------------------------------------------------ on-the-fly path on the tensor cores
 @pytest.mark.parametrize("kind", ["smooth", "rand", "int", "far", "edge"])
-@pytest.mark.parametrize("shape", [(1, 64, 24, 40, 4), (2, 128, 19, 45, 3), (1, 256, 55, 128, 4)])
+@pytest.mark.parametrize("shape", [(1, 64, 24, 40, 4), (2, 128, 19, 45, 3), (1, 256, 55, 128, 4),
+                                   # persistent kernel: several units per CTA, one level per unit / all four levels
+                                   (8, 64, 40, 64, 4), (37, 64, 16, 64, 4),
+                                   # D > 256: the per-(block, level) kernel without resident query features
+                                   (1, 320, 17, 33, 2)])
 def test_alternate_tensor_core_matches_fp32_path(shape, kind):
     """rc_alt_lookup_fwd_tc against rc_alt_lookup_fwd (fp32, itself pinned to the reference extension) fed
     bf16-rounded features: what remains is fp32 summation order.  Coordinates: a smooth flow (small
