@@ -274,6 +274,8 @@ constexpr int P_NSTAGE = 3;
 constexpr int P_MAX_KB = 4;                 // resident query features: up to 4 k-blocks = 256 channels
 constexpr int P_NDESC = 4;
 constexpr int P_TAIL_BYTES = 320;
+constexpr int P_THREADS = 320;              // warp 0 producer, warp 1 MMA, warps 2..9 epilogue (two per TMEM lane quarter)
+constexpr int HALF_W = CH_W / 2;            // accumulator columns per epilogue warp and target row
 
 struct PersistParams {
   AtcParams a;
@@ -283,17 +285,16 @@ struct PersistParams {
 struct LevelDesc { int bx0, by0, nx, ny; };
 
 template <int R>
-__global__ void __launch_bounds__(ATC_THREADS, 1)
+__global__ void __launch_bounds__(P_THREADS, 1)
 alt_tc_persist_kernel(const __grid_constant__ AtcMaps maps, const float *__restrict__ coords,
                       float *__restrict__ out, const PersistParams pp) {
   constexpr int NW = 2 * R + 1, T = 2 * R + 2, WS = T * T + 1;
   const AtcParams &p = pp.a;
-  extern __shared__ __align__(1024) uint8_t smem[];
-  if ((smem_u32(smem) & 1023u) != 0) __trap();            // the swizzled operand tiles need 1024-byte alignment
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const uint32_t sA = smem_u32(smem);                                       // P_MAX_KB x 16 KB
   const uint32_t sB = sA + P_MAX_KB * A_BYTES;                              // P_NSTAGE x 32 KB
-  float *scratch = (float *)(smem + P_MAX_KB * A_BYTES + P_NSTAGE * B_BYTES);   // 4 warps x [32 cols][32 lanes]
-  float *wins = scratch + 4 * 32 * 32;
+  float *wins = (float *)(smem + P_MAX_KB * A_BYTES + P_NSTAGE * B_BYTES);  // 128 windows x (T*T+1) floats
   uint8_t *tail = (uint8_t *)(wins + 128 * WS);
   tail = (uint8_t *)(((uintptr_t)tail + 15) & ~(uintptr_t)15);
   const uint32_t sBar = smem_u32(tail);
@@ -312,8 +313,8 @@ alt_tc_persist_kernel(const __grid_constant__ AtcMaps maps, const float *__restr
   if (threadIdx.x == 0) {
     for (int s = 0; s < P_NSTAGE; ++s) { mbar_init(b_full + 8 * s, 1); mbar_init(b_empty + 8 * s, 1); }
     for (int s = 0; s < P_MAX_KB; ++s) { mbar_init(a_full + 8 * s, 1); mbar_init(a_empty + 8 * s, 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(t_full + 8 * s, 1); mbar_init(t_empty + 8 * s, 4); }
-    for (int s = 0; s < P_NDESC; ++s) { mbar_init(d_full + 8 * s, 1); mbar_init(d_empty + 8 * s, 5); }
+    for (int s = 0; s < 2; ++s) { mbar_init(t_full + 8 * s, 1); mbar_init(t_empty + 8 * s, 8); }
+    for (int s = 0; s < P_NDESC; ++s) { mbar_init(d_full + 8 * s, 1); mbar_init(d_empty + 8 * s, 9); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -441,10 +442,12 @@ alt_tc_persist_kernel(const __grid_constant__ AtcMaps maps, const float *__restr
     }
   } else {
     // ===================================================== epilogue: pick the window taps out of every chunk
-    const int quarter = warp & 3;
+    // Two warps per TMEM lane quarter (same 32 queries): warp `half` takes accumulator columns
+    // [16*half, 16*half+16) of every target row and, afterwards, half of the output rows.
+    const int quarter = warp & 3, half = (warp - 2) >> 2;
+    const uint32_t pair_bar = 1 + quarter;                 // named barrier of the two warps of a quarter
     const int ql = quarter * 32 + lane;                    // TMEM lane = row of the A box = qy * 16 + qx
     float *w = wins + ql * WS;
-    float *scr = scratch + quarter * 32 * 32 + lane;       // column c of this lane's row sits at scr[c * 32]
     uint32_t dcount = 0, g = 0;
     // this thread's query in a unit and its coordinates, fetched one unit ahead of their use
     int q_nx = -1, b_nx = 0;
@@ -462,6 +465,10 @@ alt_tc_persist_kernel(const __grid_constant__ AtcMaps maps, const float *__restr
       }
     };
     fetch(blockIdx.x);
+    // rows of the (2r+2)-row window this warp clears, and output rows it interpolates
+    constexpr int ZSPLIT = T / 2, OSPLIT = (NW + 1) / 2;
+    const int z_begin = half ? ZSPLIT : 0, z_end = half ? T : ZSPLIT;
+    const int o_begin = half ? OSPLIT : 0, o_end = half ? NW : OSPLIT;
     for (int u = blockIdx.x; u < pp.n_units; u += gridDim.x) {
       const int lg = u / pp.n_items;                                  // fine levels (most chunks) first
       const int l_begin = lg * pp.lpu, l_end = min(p.num_levels, l_begin + pp.lpu);
@@ -472,12 +479,13 @@ alt_tc_persist_kernel(const __grid_constant__ AtcMaps maps, const float *__restr
         int x0 = 0, y0 = 0;
         float ax = 0.f, ay = 0.f;
         const bool relevant = q >= 0 && window_at_level<R>(cxf, cyf, l, p.Hl[l], p.Wl[l], x0, y0, ax, ay);
+        named_bar_sync(pair_bar, 64);                      // the partner is done reading the previous window
         // every in-map tap of a relevant window lies in some chunk and is overwritten below; only windows that
         // leave the map (or miss it) keep zeros
         if (!relevant || x0 < 0 || y0 < 0 || x0 + T > p.Wl[l] || y0 + T > p.Hl[l]) {
-#pragma unroll 4
-          for (int k = 0; k < T * T; ++k) w[k] = 0.f;
+          for (int k = z_begin * T; k < z_end * T; ++k) w[k] = 0.f;
         }
+        named_bar_sync(pair_bar, 64);                      // cleared before either warp writes taps
         const uint32_t slot = dcount % P_NDESC;
         mbar_wait(d_full + 8 * slot, (dcount / P_NDESC) & 1);
         const LevelDesc d = descs[slot];
@@ -490,44 +498,48 @@ alt_tc_persist_kernel(const __grid_constant__ AtcMaps maps, const float *__restr
           cx0 += CH_W;
           if (ccol == d.nx) { ccol = 0; cx0 = d.bx0; cy0 += CH_H; }
           ++ccol;
-          const int i_lo = max(cx0 - x0, 0), i_hi = min(cx0 + CH_W - x0, T);   // window columns inside this chunk
+          const int hx0 = cx0 + half * HALF_W;                                 // this warp's 16 target columns
+          const int i_lo = max(hx0 - x0, 0), i_hi = min(hx0 + HALF_W - x0, T); // window columns inside them
           const bool cols = relevant && i_lo < i_hi;
-          // the accumulator columns any lane of this warp wants out of the chunk
-          const int cmin = __reduce_min_sync(0xffffffffu, cols ? x0 + i_lo - cx0 : CH_W);
-          const int cmax = __reduce_max_sync(0xffffffffu, cols ? x0 + i_hi - 1 - cx0 : -1);
+          // tap i of the window sits in accumulator column sft + i of this warp's 16: the lane-dependent shift goes
+          // into the store address, a 16-bit mask says which columns are taps of this lane's window at all
+          const int sft = x0 - hx0;
+          uint32_t mask = 0;
+          if (cols) mask = (((1u << (i_hi - i_lo)) - 1u) << (sft + i_lo)) & 0xffffu;
+          const bool any_cols = __any_sync(0xffffffffu, cols);
           mbar_wait(t_full + 8 * acc, (g >> 1) & 1);
           fence_after();
-          const uint32_t taddr = tmem_base + acc * 256 + ((uint32_t)(quarter * 32) << 16);
+          const uint32_t taddr = tmem_base + acc * 256 + half * HALF_W + ((uint32_t)(quarter * 32) << 16);
+          if (any_cols) {
 #pragma unroll 1
-          for (int rr = 0; rr < CH_H; ++rr) {
-            const int j = cy0 + rr - y0;                                       // window row of this target row
-            const bool need = cols && j >= 0 && j < T;
-            if (!__any_sync(0xffffffffu, need)) continue;
-            uint32_t v[32];
-            tmem_ld32(taddr + rr * CH_W, v);
-            tmem_ld_wait();
+            for (int rr = 0; rr < CH_H; rr += 2) {
+              const int j0 = cy0 + rr - y0, j1 = j0 + 1;                       // window rows of two target rows
+              const bool need0 = cols && j0 >= 0 && j0 < T, need1 = cols && j1 >= 0 && j1 < T;
+              const bool any0 = __any_sync(0xffffffffu, need0), any1 = __any_sync(0xffffffffu, need1);
+              if (!(any0 || any1)) continue;
+              uint32_t v0[HALF_W], v1[HALF_W];
+              if (any0) tmem_ld16(taddr + rr * CH_W, v0);
+              if (any1) tmem_ld16(taddr + (rr + 1) * CH_W, v1);
+              tmem_ld_wait();
+              if (need0) {
+                float *wr = w + j0 * T - sft;
 #pragma unroll
-            for (int k8 = 0; k8 < 32; k8 += 8) {
-              if (k8 + 7 >= cmin && k8 <= cmax) {                              // warp-uniform
+                for (int k = 0; k < HALF_W; ++k)
+                  if (mask & (1u << k)) wr[k] = __uint_as_float(v0[k]);
+              }
+              if (need1) {
+                float *wr = w + j1 * T - sft;
 #pragma unroll
-                for (int k = k8; k < k8 + 8; ++k) scr[k * 32] = __uint_as_float(v[k]);
+                for (int k = 0; k < HALF_W; ++k)
+                  if (mask & (1u << k)) wr[k] = __uint_as_float(v1[k]);
               }
             }
-            __syncwarp();
-            if (need) {
-              float tv[T];
-#pragma unroll
-              for (int i = 0; i < T; ++i) tv[i] = scr[min(max(x0 + i - cx0, 0), CH_W - 1) * 32];   // all loads first
-#pragma unroll
-              for (int i = 0; i < T; ++i)
-                if (i >= i_lo && i < i_hi) w[j * T + i] = tv[i];
-            }
-            __syncwarp();
           }
           fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(t_empty + 8 * acc);
         }
+        named_bar_sync(pair_bar, 64);                      // both warps' taps are in place
 
         // ---- bilinear interpolation of the finished window; channel = l*NW*NW + i*NW + j (x slow, y fast)
         if (q >= 0) {
@@ -535,14 +547,16 @@ alt_tc_persist_kernel(const __grid_constant__ AtcMaps maps, const float *__restr
           float *op = out + ((size_t)b * C + (size_t)l * NW * NW) * N1 + q;
           float hprev[NW];
 #pragma unroll
-          for (int j = 0; j < T; ++j) {
+          for (int jj = 0; jj <= OSPLIT; ++jj) {
+            const int j = o_begin + jj;                    // window row; output row j - 1
+            if (j > o_end) break;
             float h[NW];
 #pragma unroll
             for (int i = 0; i < NW; ++i) {
               const float v0 = w[j * T + i], v1 = w[j * T + i + 1];
               h[i] = fmaf(ax, v1 - v0, v0);
             }
-            if (j > 0) {
+            if (jj > 0) {
 #pragma unroll
               for (int i = 0; i < NW; ++i)
                 op[(size_t)(i * NW + (j - 1)) * N1] = fmaf(ay, h[i] - hprev[i], hprev[i]) * p.out_scale;
@@ -551,7 +565,6 @@ alt_tc_persist_kernel(const __grid_constant__ AtcMaps maps, const float *__restr
             for (int i = 0; i < NW; ++i) hprev[i] = h[i];
           }
         }
-        __syncwarp();
       }
     }
   }
@@ -652,13 +665,13 @@ int alt_tc_launch_persistent(const AtcMaps &maps, const float *coords, float *ou
   }
   pp.n_units = (int)units;
   pp.n_items = (int)items;
-  const size_t smem = (size_t)P_MAX_KB * A_BYTES + (size_t)P_NSTAGE * B_BYTES + 4 * 32 * 32 * sizeof(float) +
+  const size_t smem = 1024 + (size_t)P_MAX_KB * A_BYTES + (size_t)P_NSTAGE * B_BYTES +
                       128 * (T * T + 1) * sizeof(float) + P_TAIL_BYTES;
   auto kern = alt_tc_persist_kernel<R>;
   RC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int grid = (int)(units < sms ? units : sms);
   if (grid == 0) return RC_OK;
-  kern<<<grid, ATC_THREADS, smem, s>>>(maps, coords, out, pp);
+  kern<<<grid, P_THREADS, smem, s>>>(maps, coords, out, pp);
   RC_LAUNCH_CHECK("alt_tc_persist_kernel");
   return RC_OK;
 }

@@ -19,13 +19,12 @@ def main():
     cur = None
     files = '?'
     total = 0
-    seen_fn = 0
+    seen_files = set()
     for r in rows:
-        if r and r[0] == "Function Name":
-            seen_fn += 1
-            if seen_fn > 1:
-                break       # first launch only
         if r and r[0] == "File Path":
+            if r[1] in seen_files:
+                break       # first launch only (a kernel's sections repeat per launch, one per source file)
+            seen_files.add(r[1])
             files = r[1].split("/")[-1]
         if r and r[0] == "Line No":
             hdr = r
