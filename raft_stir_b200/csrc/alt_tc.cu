@@ -15,10 +15,13 @@
 // only slower.  Both operands come in through TMA boxes of the NHWC feature maps; coordinates
 // outside a map arrive as zeros, which IS grid_sample's zeros padding.
 //
-// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = MMA issuer + TMEM owner, warps 2..5 =
-// epilogue (thread = query = TMEM lane).  Per chunk the epilogue reads the accumulator one target
-// row (32 columns) at a time, bounces it through a per-warp shared-memory scratch and lets every
-// lane pick the <= (2r+2) taps of its own window row; the windows collect in shared memory and are
+// Two kernels.  alt_tc_persist_kernel (D <= 256, every configuration the reference ships) is the
+// one that runs: persistent CTAs, query features resident per work unit, see the comment above it.
+// alt_tc_fwd_kernel is the first version, kept for D > 256: one CTA per (query block, level),
+// 192 threads: warp 0 = TMA producer, warp 1 = MMA issuer + TMEM owner, warps 2..5 = epilogue
+// (thread = query = TMEM lane).  Per chunk its epilogue reads the accumulator one target row
+// (32 columns) at a time, bounces it through a per-warp shared-memory scratch and lets every lane
+// pick the <= (2r+2) taps of its own window row; the windows collect in shared memory and are
 // interpolated once all chunks are done.  Two TMEM accumulators alternate, so the MMAs of chunk c+1
 // run while chunk c is picked apart.
 #include "common.cuh"
@@ -261,49 +264,80 @@ alt_tc_fwd_kernel(const __grid_constant__ AtcMaps maps, const float *__restrict_
 //
 // The kernel above reloads the query block's features with every k-block of every chunk, and every
 // CTA pays its own prologue (barrier init, TMEM allocation, coordinates, pipeline fill) for two or
-// three chunks of work: at a full batch it is bound by the L2 -> shared-memory traffic (192 KB per
-// chunk against 2048 tensor-core cycles) and by those bubbles.  Here one CTA per SM walks a list
-// of work units; a unit is one 8 x 16 query block and a run of pyramid levels.  The block's own
-// features (128 x D bf16, up to 64 KB) are loaded ONCE per unit and stay in shared memory while the
-// chunks of all its levels stream through a 3-stage ring, so a chunk costs 128 KB of L2 traffic
-// instead of 192; the producer warp works out the bounding boxes of the coming levels itself and
+// three chunks of work.  Here one CTA per SM walks a list of work units; a unit is one 8 x 16 query
+// block and a run of pyramid levels.  The block's own features (128 x D bf16, up to 64 KB) are
+// loaded ONCE per unit and stay in shared memory while the chunks of all its levels stream through
+// a 3-slot ring; the producer warp works out the bounding boxes of the coming levels itself and
 // hands them to the other warps through a small descriptor ring, so loads, MMAs and tap picking of
-// consecutive levels and units overlap without a CTA-wide barrier.  The bounce scratch is stored
-// column-major (one bank per lane), which makes the tap picking free of bank conflicts.
-constexpr int P_NSTAGE = 3;
+// consecutive levels and units overlap without a CTA-wide barrier.  Chunks are cut to the box
+// (ChunkWalk below).  Eight epilogue warps, two per TMEM lane quarter: each reads 16 accumulator
+// columns of a target row and stores them straight into its query's window, the lane-dependent
+// horizontal shift folded into the store address (no bounce buffer, no intra-warp barrier).
+constexpr int P_SLOT_N = 256;               // most targets of one chunk (accumulator columns, rows of a ring slot);
+                                            // 128 (six 16 KB slots, four accumulators) measured 23 % slower
+constexpr int P_SLOT_BYTES = P_SLOT_N * 128;
+constexpr int P_NSTAGE = 96 * 1024 / P_SLOT_BYTES;
+constexpr int P_NACC = 512 / P_SLOT_N;      // accumulators in TMEM
+constexpr int HALF_W = CH_W / 2;            // accumulator columns per epilogue warp and target row; narrow chunk width
 constexpr int P_MAX_KB = 4;                 // resident query features: up to 4 k-blocks = 256 channels
 constexpr int P_NDESC = 4;
-constexpr int P_TAIL_BYTES = 320;
+constexpr int P_TAIL_BYTES = 16 * P_NSTAGE + 16 * P_MAX_KB + 16 * P_NACC + 16 * P_NDESC + 16 + 16 * P_NDESC + 16;
 constexpr int P_THREADS = 320;              // warp 0 producer, warp 1 MMA, warps 2..9 epilogue (two per TMEM lane quarter)
-constexpr int HALF_W = CH_W / 2;            // accumulator columns per epilogue warp and target row
 
 struct PersistParams {
   AtcParams a;
   int n_units, n_items, nsplit, lpu;        // items = B * blocks; units = items * nsplit; lpu = levels per unit
 };
 
-struct LevelDesc { int bx0, by0, nx, ny; };
+// Bounding box of a unit's windows in one level, as the producer warp publishes it.
+struct LevelDesc { int bx0, by0, bw, bh; };
+
+struct PersistMaps {
+  CUtensorMap f1;                     // fmap1 NHWC bf16: (D, W, H, B), box (64, 16, 8, 1)
+  CUtensorMap f2w[RC_MAX_LEVELS];     // fmap2 level l: box (64, 32, 2, 1): two target rows of a wide chunk
+  CUtensorMap f2n[RC_MAX_LEVELS];     // fmap2 level l: box (64, 16, 2, 1): two target rows of a narrow chunk
+};
+
+// The chunks of one level, derived from its box the same way by all three roles.  A box at most 16 targets wide
+// (the coarse levels of a smooth flow) is cut into chunks of 16 x (2..16) targets, a wider one into 32 x (2..8);
+// rows come in twos (the TMA box), so the accumulator of a chunk has N = 32 .. 256 columns and neither the loads
+// nor the MMAs are spent on targets far outside the box.
+struct ChunkWalk {
+  int cw, rows_max, nx, ny, bh;
+  bool narrow;
+  __device__ explicit ChunkWalk(const LevelDesc &d) {
+    narrow = d.bw <= HALF_W;
+    cw = narrow ? HALF_W : CH_W;
+    rows_max = P_SLOT_N / cw;
+    bh = d.bh;
+    const bool some = d.bw > 0 && d.bh > 0;
+    nx = some ? (d.bw + cw - 1) / cw : 0;
+    ny = some ? (d.bh + rows_max - 1) / rows_max : 0;
+  }
+  __device__ int rows(int iy) const { return min(rows_max, (bh - iy * rows_max + 1) & ~1); }
+};
 
 template <int R>
 __global__ void __launch_bounds__(P_THREADS, 1)
-alt_tc_persist_kernel(const __grid_constant__ AtcMaps maps, const float *__restrict__ coords,
+alt_tc_persist_kernel(const __grid_constant__ PersistMaps maps, const float *__restrict__ coords,
                       float *__restrict__ out, const PersistParams pp) {
   constexpr int NW = 2 * R + 1, T = 2 * R + 2, WS = T * T + 1;
   const AtcParams &p = pp.a;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const uint32_t sA = smem_u32(smem);                                       // P_MAX_KB x 16 KB
-  const uint32_t sB = sA + P_MAX_KB * A_BYTES;                              // P_NSTAGE x 32 KB
-  float *wins = (float *)(smem + P_MAX_KB * A_BYTES + P_NSTAGE * B_BYTES);  // 128 windows x (T*T+1) floats
+  const uint32_t sB = sA + P_MAX_KB * A_BYTES;                              // P_NSTAGE ring slots
+  float *wins = (float *)(smem + P_MAX_KB * A_BYTES + P_NSTAGE * P_SLOT_BYTES);  // 128 windows x (T*T+1) floats
   uint8_t *tail = (uint8_t *)(wins + 128 * WS);
   tail = (uint8_t *)(((uintptr_t)tail + 15) & ~(uintptr_t)15);
   const uint32_t sBar = smem_u32(tail);
-  const uint32_t b_full = sBar, b_empty = sBar + 8 * P_NSTAGE;              // 3 + 3
-  const uint32_t a_full = sBar + 48, a_empty = a_full + 8 * P_MAX_KB;       // 4 + 4
-  const uint32_t t_full = sBar + 112, t_empty = t_full + 16;                // 2 + 2
-  const uint32_t d_full = sBar + 144, d_empty = d_full + 8 * P_NDESC;       // 4 + 4
-  uint32_t *tmem_slot = (uint32_t *)(tail + 208);
-  LevelDesc *descs = (LevelDesc *)(tail + 224);                             // P_NDESC x 16 B
+  const uint32_t b_full = sBar, b_empty = b_full + 8 * P_NSTAGE;
+  const uint32_t a_full = b_empty + 8 * P_NSTAGE, a_empty = a_full + 8 * P_MAX_KB;
+  const uint32_t t_full = a_empty + 8 * P_MAX_KB, t_empty = t_full + 8 * P_NACC;
+  const uint32_t d_full = t_empty + 8 * P_NACC, d_empty = d_full + 8 * P_NDESC;
+  constexpr int BAR_BYTES = 16 * P_NSTAGE + 16 * P_MAX_KB + 16 * P_NACC + 16 * P_NDESC;
+  uint32_t *tmem_slot = (uint32_t *)(tail + BAR_BYTES);
+  LevelDesc *descs = (LevelDesc *)(tail + BAR_BYTES + 16);                  // P_NDESC x 16 B
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int N1 = p.H * p.W;
@@ -313,7 +347,7 @@ alt_tc_persist_kernel(const __grid_constant__ AtcMaps maps, const float *__restr
   if (threadIdx.x == 0) {
     for (int s = 0; s < P_NSTAGE; ++s) { mbar_init(b_full + 8 * s, 1); mbar_init(b_empty + 8 * s, 1); }
     for (int s = 0; s < P_MAX_KB; ++s) { mbar_init(a_full + 8 * s, 1); mbar_init(a_empty + 8 * s, 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(t_full + 8 * s, 1); mbar_init(t_empty + 8 * s, 8); }
+    for (int s = 0; s < P_NACC; ++s) { mbar_init(t_full + 8 * s, 1); mbar_init(t_empty + 8 * s, 8); }
     for (int s = 0; s < P_NDESC; ++s) { mbar_init(d_full + 8 * s, 1); mbar_init(d_empty + 8 * s, 9); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -371,23 +405,26 @@ alt_tc_persist_kernel(const __grid_constant__ AtcMaps maps, const float *__restr
         mny = __reduce_min_sync(0xffffffffu, mny);
         mxx = __reduce_max_sync(0xffffffffu, mxx);
         mxy = __reduce_max_sync(0xffffffffu, mxy);
-        const int nx = mxx >= mnx ? (mxx - mnx) / CH_W + 1 : 0;
-        const int ny = mxy >= mny ? (mxy - mny) / CH_H + 1 : 0;
         if (lane == 0) {
+          const LevelDesc d{mnx, mny, mxx >= mnx ? mxx - mnx + 1 : 0, mxy >= mny ? mxy - mny + 1 : 0};
           const uint32_t slot = dcount % P_NDESC;
           mbar_wait(d_empty + 8 * slot, ((dcount / P_NDESC) & 1) ^ 1);
-          descs[slot] = LevelDesc{mnx, mny, nx, ny};
+          descs[slot] = d;
           mbar_arrive(d_full + 8 * slot);
-          int cx0 = mnx - CH_W, cy0 = mny, ccol = 0;
-          for (int c = 0; c < nx * ny; ++c) {
-            cx0 += CH_W;
-            if (ccol == nx) { ccol = 0; cx0 = mnx; cy0 += CH_H; }
-            ++ccol;
-            for (int kb = 0; kb < NKB; ++kb) {
-              mbar_wait(b_empty + 8 * st, ph ^ 1);
-              mbar_expect_tx(b_full + 8 * st, B_BYTES);
-              tma_load_4d(sB + st * B_BYTES, &maps.f2[l], b_full + 8 * st, kb * KB, cx0, cy0, b);
-              if (++st == P_NSTAGE) { st = 0; ph ^= 1; }
+          const ChunkWalk cwk(d);
+          const CUtensorMap *map = cwk.narrow ? &maps.f2n[l] : &maps.f2w[l];
+          const uint32_t pair_bytes = 2 * cwk.cw * 128;                 // two target rows of one k-block
+          for (int iy = 0; iy < cwk.ny; ++iy) {
+            const int rows = cwk.rows(iy), cy0 = d.by0 + iy * cwk.rows_max;
+            for (int ix = 0; ix < cwk.nx; ++ix) {
+              const int cx0 = d.bx0 + ix * cwk.cw;
+              for (int kb = 0; kb < NKB; ++kb) {
+                mbar_wait(b_empty + 8 * st, ph ^ 1);
+                mbar_expect_tx(b_full + 8 * st, (rows / 2) * pair_bytes);
+                for (int r2 = 0; r2 < rows / 2; ++r2)
+                  tma_load_4d(sB + st * P_SLOT_BYTES + r2 * pair_bytes, map, b_full + 8 * st, kb * KB, cx0, cy0 + 2 * r2, b);
+                if (++st == P_NSTAGE) { st = 0; ph ^= 1; }
+              }
             }
           }
         }
@@ -398,7 +435,6 @@ alt_tc_persist_kernel(const __grid_constant__ AtcMaps maps, const float *__restr
   } else if (warp == 1) {
     // ===================================================== MMA issuer
     if (lane == 0) {
-      constexpr uint32_t IDESC = idesc_bf16(128, 256);
       uint32_t st = 0, ph = 0, dcount = 0, nu = 0, g = 0;
       for (int u = blockIdx.x; u < pp.n_units; u += gridDim.x, ++nu) {
         const int lg = u / pp.n_items;
@@ -407,21 +443,24 @@ alt_tc_persist_kernel(const __grid_constant__ AtcMaps maps, const float *__restr
         for (int l = l_begin; l < l_end; ++l, ++dcount) {
           const uint32_t slot = dcount % P_NDESC;
           mbar_wait(d_full + 8 * slot, (dcount / P_NDESC) & 1);
-          const int nchunks = descs[slot].nx * descs[slot].ny;
+          const ChunkWalk cwk(descs[slot]);
           mbar_arrive(d_empty + 8 * slot);
-          for (int c = 0; c < nchunks; ++c, ++g) {
-            const uint32_t acc = g & 1;
+          const int nchunks = cwk.nx * cwk.ny;
+          for (int c = 0, ix = 0, iy = 0; c < nchunks; ++c, ++g) {
+            const uint32_t acc = g % P_NACC;
             const bool last = (l == l_end - 1) && (c == nchunks - 1);
-            mbar_wait(t_empty + 8 * acc, ((g >> 1) & 1) ^ 1);
+            const uint32_t IDESC = idesc_bf16(128, cwk.rows(iy) * cwk.cw);     // N = targets of this chunk
+            if (++ix == cwk.nx) { ix = 0; ++iy; }
+            mbar_wait(t_empty + 8 * acc, ((g / P_NACC) & 1) ^ 1);
             fence_after();
             for (int kb = 0; kb < NKB; ++kb) {
               if (first) mbar_wait(a_full + 8 * kb, nu & 1);
               mbar_wait(b_full + 8 * st, ph);
               fence_after();
-              const uint32_t al = desc_lo(sA + kb * A_BYTES), bl = desc_lo(sB + st * B_BYTES);
+              const uint32_t al = desc_lo(sA + kb * A_BYTES), bl = desc_lo(sB + st * P_SLOT_BYTES);
 #pragma unroll
               for (int k = 0; k < 4; ++k)
-                umma_bf16(tmem_base + acc * 256, desc_make(al + 2 * k), desc_make(bl + 2 * k), IDESC, (kb | k) != 0);
+                umma_bf16(tmem_base + acc * P_SLOT_N, desc_make(al + 2 * k), desc_make(bl + 2 * k), IDESC, (kb | k) != 0);
               umma_commit(b_empty + 8 * st);
               if (last) umma_commit(a_empty + 8 * kb);      // this resident k-block is free once its MMAs are done
               if (++st == P_NSTAGE) { st = 0; ph ^= 1; }
@@ -491,53 +530,57 @@ alt_tc_persist_kernel(const __grid_constant__ AtcMaps maps, const float *__restr
         const LevelDesc d = descs[slot];
         __syncwarp();
         if (lane == 0) mbar_arrive(d_empty + 8 * slot);
-        const int nchunks = d.nx * d.ny;
-        int cx0 = d.bx0 - CH_W, cy0 = d.by0, ccol = 0;
-        for (int c = 0; c < nchunks; ++c, ++g) {
-          const uint32_t acc = g & 1;
-          cx0 += CH_W;
-          if (ccol == d.nx) { ccol = 0; cx0 = d.bx0; cy0 += CH_H; }
-          ++ccol;
-          const int hx0 = cx0 + half * HALF_W;                                 // this warp's 16 target columns
-          const int i_lo = max(hx0 - x0, 0), i_hi = min(hx0 + HALF_W - x0, T); // window columns inside them
-          const bool cols = relevant && i_lo < i_hi;
-          // tap i of the window sits in accumulator column sft + i of this warp's 16: the lane-dependent shift goes
-          // into the store address, a 16-bit mask says which columns are taps of this lane's window at all
-          const int sft = x0 - hx0;
-          uint32_t mask = 0;
-          if (cols) mask = (((1u << (i_hi - i_lo)) - 1u) << (sft + i_lo)) & 0xffffu;
-          const bool any_cols = __any_sync(0xffffffffu, cols);
-          mbar_wait(t_full + 8 * acc, (g >> 1) & 1);
-          fence_after();
-          const uint32_t taddr = tmem_base + acc * 256 + half * HALF_W + ((uint32_t)(quarter * 32) << 16);
-          if (any_cols) {
+        const ChunkWalk cwk(d);
+        // wide chunk: this warp takes columns [16*half, +16) of every target row; narrow chunk (16 columns): every
+        // other row.  Either way one tcgen05.ld of 16 columns per target row.
+        const int coff = cwk.narrow ? 0 : half * HALF_W;
+        const int rstep = cwk.narrow ? 2 : 1, rr0 = cwk.narrow ? half : 0;
+        for (int iy = 0; iy < cwk.ny; ++iy) {
+          const int rows = cwk.rows(iy), cy0 = d.by0 + iy * cwk.rows_max;
+          for (int ix = 0; ix < cwk.nx; ++ix, ++g) {
+            const uint32_t acc = g % P_NACC;
+            const int hx0 = d.bx0 + ix * cwk.cw + coff;                          // x of this warp's 16 target columns
+            const int i_lo = max(hx0 - x0, 0), i_hi = min(hx0 + HALF_W - x0, T); // window columns inside them
+            const bool cols = relevant && i_lo < i_hi;
+            // tap i of the window sits in accumulator column sft + i of these 16: the lane-dependent shift goes
+            // into the store address, a 16-bit mask says which columns are taps of this lane's window at all
+            const int sft = x0 - hx0;
+            uint32_t mask = 0;
+            if (cols) mask = (((1u << (i_hi - i_lo)) - 1u) << (sft + i_lo)) & 0xffffu;
+            const bool any_cols = __any_sync(0xffffffffu, cols);
+            mbar_wait(t_full + 8 * acc, (g / P_NACC) & 1);
+            fence_after();
+            const uint32_t taddr = tmem_base + acc * P_SLOT_N + coff + ((uint32_t)(quarter * 32) << 16);
+            if (any_cols) {
 #pragma unroll 1
-            for (int rr = 0; rr < CH_H; rr += 2) {
-              const int j0 = cy0 + rr - y0, j1 = j0 + 1;                       // window rows of two target rows
-              const bool need0 = cols && j0 >= 0 && j0 < T, need1 = cols && j1 >= 0 && j1 < T;
-              const bool any0 = __any_sync(0xffffffffu, need0), any1 = __any_sync(0xffffffffu, need1);
-              if (!(any0 || any1)) continue;
-              uint32_t v0[HALF_W], v1[HALF_W];
-              if (any0) tmem_ld16(taddr + rr * CH_W, v0);
-              if (any1) tmem_ld16(taddr + (rr + 1) * CH_W, v1);
-              tmem_ld_wait();
-              if (need0) {
-                float *wr = w + j0 * T - sft;
+              for (int rr = rr0; rr < rows; rr += 2 * rstep) {
+                const int ra = rr, rb = rr + rstep;                              // two target rows per step
+                const int j0 = cy0 + ra - y0, j1 = cy0 + rb - y0;                // their window rows
+                const bool need0 = cols && j0 >= 0 && j0 < T, need1 = cols && rb < rows && j1 >= 0 && j1 < T;
+                const bool any0 = __any_sync(0xffffffffu, need0), any1 = __any_sync(0xffffffffu, need1);
+                if (!(any0 || any1)) continue;
+                uint32_t v0[HALF_W], v1[HALF_W];
+                if (any0) tmem_ld16(taddr + ra * cwk.cw, v0);
+                if (any1) tmem_ld16(taddr + rb * cwk.cw, v1);
+                tmem_ld_wait();
+                if (need0) {
+                  float *wr = w + j0 * T - sft;
 #pragma unroll
-                for (int k = 0; k < HALF_W; ++k)
-                  if (mask & (1u << k)) wr[k] = __uint_as_float(v0[k]);
-              }
-              if (need1) {
-                float *wr = w + j1 * T - sft;
+                  for (int k = 0; k < HALF_W; ++k)
+                    if (mask & (1u << k)) wr[k] = __uint_as_float(v0[k]);
+                }
+                if (need1) {
+                  float *wr = w + j1 * T - sft;
 #pragma unroll
-                for (int k = 0; k < HALF_W; ++k)
-                  if (mask & (1u << k)) wr[k] = __uint_as_float(v1[k]);
+                  for (int k = 0; k < HALF_W; ++k)
+                    if (mask & (1u << k)) wr[k] = __uint_as_float(v1[k]);
+                }
               }
             }
+            fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(t_empty + 8 * acc);
           }
-          fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(t_empty + 8 * acc);
         }
         named_bar_sync(pair_bar, 64);                      // both warps' taps are in place
 
@@ -642,7 +685,7 @@ int alt_tc_launch(const AtcMaps &maps, const float *coords, float *out, const At
 // Work split of the persistent kernel: a unit is a query block with num_levels / nsplit levels.  One unit per
 // block keeps the block's features resident longest; small batches are cut finer so that every SM has work.
 template <int R>
-int alt_tc_launch_persistent(const AtcMaps &maps, const float *coords, float *out, const AtcParams &p,
+int alt_tc_launch_persistent(const PersistMaps &maps, const float *coords, float *out, const AtcParams &p,
                              cudaStream_t s) {
   constexpr int T = 2 * R + 2;
   int dev = 0, sms = 0;
@@ -665,7 +708,7 @@ int alt_tc_launch_persistent(const AtcMaps &maps, const float *coords, float *ou
   }
   pp.n_units = (int)units;
   pp.n_items = (int)items;
-  const size_t smem = 1024 + (size_t)P_MAX_KB * A_BYTES + (size_t)P_NSTAGE * B_BYTES +
+  const size_t smem = 1024 + (size_t)P_MAX_KB * A_BYTES + (size_t)P_NSTAGE * P_SLOT_BYTES +
                       128 * (T * T + 1) * sizeof(float) + P_TAIL_BYTES;
   auto kern = alt_tc_persist_kernel<R>;
   RC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -674,12 +717,6 @@ int alt_tc_launch_persistent(const AtcMaps &maps, const float *coords, float *ou
   kern<<<grid, P_THREADS, smem, s>>>(maps, coords, out, pp);
   RC_LAUNCH_CHECK("alt_tc_persist_kernel");
   return RC_OK;
-}
-
-template <int R>
-int alt_tc_dispatch(const AtcMaps &maps, const float *coords, float *out, const AtcParams &p, cudaStream_t s) {
-  if (p.D <= P_MAX_KB * KB) return alt_tc_launch_persistent<R>(maps, coords, out, p, s);
-  return alt_tc_launch<R>(maps, coords, out, p, s);
 }
 
 }  // namespace
@@ -699,20 +736,37 @@ int launch_alt_lookup_tc(const void *f1_bf16, const void *f2_pyr_bf16, const flo
   p.B = B; p.D = D; p.H = H; p.W = W; p.num_levels = num_levels;
   p.nbx = ceil_div(W, QB_W); p.nby = ceil_div(H, QB_H);
   p.out_scale = 1.0f / sqrtf((float)D);
-  AtcMaps maps;
-  int r = encode_nhwc(&maps.f1, f1_bf16, B, D, H, W, QB_W, QB_H);
-  if (r) return r;
   for (int l = 0; l < RC_MAX_LEVELS; ++l) {
     const int ll = l < num_levels ? l : 0;
     p.Hl[l] = H >> ll; p.Wl[l] = W >> ll;
-    r = encode_nhwc(&maps.f2[l], (const __nv_bfloat16 *)f2_pyr_bf16 + off[ll], B, D, H >> ll, W >> ll, CH_W, CH_H);
-    if (r) return r;
   }
+  auto level = [&](int l) { return (const __nv_bfloat16 *)f2_pyr_bf16 + off[l < num_levels ? l : 0]; };
+  int r;
+  if (D <= P_MAX_KB * KB) {
+    // persistent kernel: query features resident, fmap2 in boxes of two target rows (32 or 16 targets wide)
+    PersistMaps maps;
+    if ((r = encode_nhwc(&maps.f1, f1_bf16, B, D, H, W, QB_W, QB_H))) return r;
+    for (int l = 0; l < RC_MAX_LEVELS; ++l) {
+      if ((r = encode_nhwc(&maps.f2w[l], level(l), B, D, p.Hl[l], p.Wl[l], CH_W, 2))) return r;
+      if ((r = encode_nhwc(&maps.f2n[l], level(l), B, D, p.Hl[l], p.Wl[l], HALF_W, 2))) return r;
+    }
+    switch (radius) {
+      case 1: return alt_tc_launch_persistent<1>(maps, coords, out, p, s);
+      case 2: return alt_tc_launch_persistent<2>(maps, coords, out, p, s);
+      case 3: return alt_tc_launch_persistent<3>(maps, coords, out, p, s);
+      case 4: return alt_tc_launch_persistent<4>(maps, coords, out, p, s);
+      default: set_error("radius %d unsupported (1..4)", radius); return RC_EINVAL;
+    }
+  }
+  AtcMaps maps;
+  if ((r = encode_nhwc(&maps.f1, f1_bf16, B, D, H, W, QB_W, QB_H))) return r;
+  for (int l = 0; l < RC_MAX_LEVELS; ++l)
+    if ((r = encode_nhwc(&maps.f2[l], level(l), B, D, p.Hl[l], p.Wl[l], CH_W, CH_H))) return r;
   switch (radius) {
-    case 1: return alt_tc_dispatch<1>(maps, coords, out, p, s);
-    case 2: return alt_tc_dispatch<2>(maps, coords, out, p, s);
-    case 3: return alt_tc_dispatch<3>(maps, coords, out, p, s);
-    case 4: return alt_tc_dispatch<4>(maps, coords, out, p, s);
+    case 1: return alt_tc_launch<1>(maps, coords, out, p, s);
+    case 2: return alt_tc_launch<2>(maps, coords, out, p, s);
+    case 3: return alt_tc_launch<3>(maps, coords, out, p, s);
+    case 4: return alt_tc_launch<4>(maps, coords, out, p, s);
     default: set_error("radius %d unsupported (1..4)", radius); return RC_EINVAL;
   }
 }
