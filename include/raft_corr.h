@@ -222,6 +222,26 @@ RC_API int rc_alt_features_bf16(const float *fmap1_nhwc, const float *fmap2_pyr,
 RC_API int rc_alt_lookup_fwd_tc(const void *fmap1_bf16, const void *fmap2_pyr_bf16, const float *coords, int B,
                          int D, int H, int W, int num_levels, int radius, float *out, rc_stream_t stream);
 
+/*
+ * Flow upsampling to full resolution, the step after the lookup + update block in every refinement
+ * iteration.
+ *   rc_upsample_flow      replaces RAFT.upsample_flow (core/raft.py:72-83): softmax over the 9 neighbours of the
+ *                         576-channel mask (channel = k*64 + sy*8 + sx), convex combination of the 3x3
+ *                         neighbourhood of 8*flow (zeros outside the map), output pixel (8y+sy, 8x+sx); one
+ *                         kernel instead of softmax + unfold + multiply + sum + permute
+ *   rc_upsample_flow_bwd  what autograd derives for it: d/dflow [B,2,H,W] (overwritten) and d/dmask [B,576,H,W]
+ *   rc_upflow8 / _bwd     replace upflow8 (core/utils/utils.py:80-82): 8 * bilinear x8, align_corners=True
+ *                         (the path RAFT-small takes, core/raft.py:133)
+ *   flow : fp32 [B, 2, H, W] (rc_upflow8: [B, C, H, W]);  mask: fp32 [B, 576, H, W]
+ *   out / gout : fp32 [B, 2, 8H, 8W].  All contiguous.  No workspace, nothing allocated.
+ */
+RC_API int rc_upsample_flow(const float *flow, const float *mask, int B, int H, int W, float *out,
+                     rc_stream_t stream);
+RC_API int rc_upsample_flow_bwd(const float *flow, const float *mask, const float *gout, int B, int H, int W,
+                         float *dflow, float *dmask, rc_stream_t stream);
+RC_API int rc_upflow8(const float *flow, int B, int C, int H, int W, float *out, rc_stream_t stream);
+RC_API int rc_upflow8_bwd(const float *gout, int B, int C, int H, int W, float *dflow, rc_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

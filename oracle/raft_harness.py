@@ -60,7 +60,7 @@ class TorchCorrBlock:
 
 
 @torch.no_grad()
-def raft_forward(nets, image1, image2, iters=12, corr_cls=TorchCorrBlock, last_only=True):
+def raft_forward(nets, image1, image2, iters=12, corr_cls=TorchCorrBlock, last_only=True, upsample_fn=None):
     """RAFT.forward(test_mode=True) (core/raft.py:86-144) -> (flow_low, flow_up)."""
     fnet, cnet, update = nets
     image1 = (2 * (image1 / 255.0) - 1.0).contiguous()
@@ -82,11 +82,11 @@ def raft_forward(nets, image1, image2, iters=12, corr_cls=TorchCorrBlock, last_o
         net, up_mask, delta = update(net, inp, corr, coords1 - coords0)
         coords1 = coords1 + delta
         if not last_only or it == iters - 1:
-            flow_up = upsample_flow(coords1 - coords0, up_mask)   # the reference upsamples every iteration
+            flow_up = (upsample_fn or upsample_flow)(coords1 - coords0, up_mask)   # the reference: every iteration
     return coords1 - coords0, flow_up
 
 
-def raft_forward_train(nets, image1, image2, iters=12, corr_cls=TorchCorrBlock):
+def raft_forward_train(nets, image1, image2, iters=12, corr_cls=TorchCorrBlock, upsample_fn=None):
     """RAFT.forward(test_mode=False) (core/raft.py:86-144): the list of upsampled flow predictions, with
     autograd history.  coords1 is detached every iteration exactly as the reference does (:123)."""
     fnet, cnet, update = nets
@@ -107,7 +107,7 @@ def raft_forward_train(nets, image1, image2, iters=12, corr_cls=TorchCorrBlock):
         corr = corr_fn(coords1)
         net, up_mask, delta = update(net, inp, corr, coords1 - coords0)
         coords1 = coords1 + delta
-        preds.append(upsample_flow(coords1 - coords0, up_mask))
+        preds.append((upsample_fn or upsample_flow)(coords1 - coords0, up_mask))
     return preds
 
 

@@ -8,5 +8,7 @@ without a CUDA tensor raises.
 """
 from .corr import AlternateCorrBlock, CorrBlock, coords_grid, install_into  # noqa: F401
 from . import alt_cuda_corr  # noqa: F401
+from .upsample import upflow8, upsample_flow  # noqa: F401
 
-__all__ = ["CorrBlock", "AlternateCorrBlock", "alt_cuda_corr", "coords_grid", "install_into"]
+__all__ = ["CorrBlock", "AlternateCorrBlock", "alt_cuda_corr", "coords_grid", "install_into", "upsample_flow",
+           "upflow8"]

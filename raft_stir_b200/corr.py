@@ -280,7 +280,14 @@ class AlternateCorrBlock:
         return out
 
 
-def install_into(raft_module) -> None:
-    """Swap the two names `core/raft.py:8` imports, e.g. install_into(sys.modules['raft'])."""
+def install_into(raft_module, upsampling: bool = True) -> None:
+    """Swap the two names `core/raft.py:8` imports, e.g. install_into(sys.modules['raft']); with `upsampling`
+    also rebind the flow upsampling that follows every iteration (core/raft.py:72-83, :133-135)."""
     raft_module.CorrBlock = CorrBlock
     raft_module.AlternateCorrBlock = AlternateCorrBlock
+    if upsampling:
+        from . import upsample as _up
+        if hasattr(raft_module, "RAFT"):
+            raft_module.RAFT.upsample_flow = lambda self, flow, mask: _up.upsample_flow(flow, mask)
+        if hasattr(raft_module, "upflow8"):
+            raft_module.upflow8 = _up.upflow8

@@ -33,6 +33,12 @@ int launch_alt_pool(const float *fmap1, const float *fmap2, int B, int D, int H,
 int launch_alt_features_bf16(const float *src, void *dst, long long elems, cudaStream_t s);
 int launch_alt_lookup_tc(const void *f1_bf16, const void *f2_pyr_bf16, const float *coords, int B, int D, int H,
                          int W, int num_levels, int radius, const int64_t *off, float *out, cudaStream_t s);
+// upsample.cu
+int launch_upsample_flow(const float *flow, const float *mask, int B, int H, int W, float *out, cudaStream_t s);
+int launch_upsample_flow_bwd(const float *flow, const float *mask, const float *gout, int B, int H, int W,
+                             float *dflow, float *dmask, cudaStream_t s);
+int launch_upflow8(const float *flow, int B, int C, int H, int W, float *out, cudaStream_t s);
+int launch_upflow8_bwd(const float *gout, int B, int C, int H, int W, float *dflow, cudaStream_t s);
 // build_bwd.cu
 int64_t build_bwd_workspace_bytes(int B, int D, int H, int W, int num_levels);
 int launch_build_bwd(const float *grad_pyramid, const float *fmap1, const float *fmap2, int B, int D,
@@ -298,6 +304,33 @@ int rc_alt_lookup_fwd_tc(const void *fmap1_bf16, const void *fmap2_pyr_bf16, con
   RC_REQUIRE((H >> (num_levels - 1)) >= 1 && (W >> (num_levels - 1)) >= 1, "map too small for %d levels", num_levels);
   return launch_alt_lookup_tc(fmap1_bf16, fmap2_pyr_bf16, coords, B, D, H, W, num_levels, radius, off, out,
                               (cudaStream_t)stream);
+}
+
+int rc_upsample_flow(const float *flow, const float *mask, int B, int H, int W, float *out, rc_stream_t stream) {
+  RC_REQUIRE(flow && mask && out, "rc_upsample_flow: NULL pointer");
+  RC_REQUIRE(B >= 1 && B <= 65535 && H >= 1 && H <= 65535 && W >= 1, "rc_upsample_flow: bad sizes B=%d H=%d W=%d", B, H, W);
+  return launch_upsample_flow(flow, mask, B, H, W, out, (cudaStream_t)stream);
+}
+
+int rc_upsample_flow_bwd(const float *flow, const float *mask, const float *gout, int B, int H, int W, float *dflow,
+                         float *dmask, rc_stream_t stream) {
+  RC_REQUIRE(flow && mask && gout && dflow && dmask, "rc_upsample_flow_bwd: NULL pointer");
+  RC_REQUIRE(B >= 1 && B <= 65535 && H >= 1 && H <= 65535 && W >= 1, "rc_upsample_flow_bwd: bad sizes B=%d H=%d W=%d", B, H, W);
+  return launch_upsample_flow_bwd(flow, mask, gout, B, H, W, dflow, dmask, (cudaStream_t)stream);
+}
+
+int rc_upflow8(const float *flow, int B, int C, int H, int W, float *out, rc_stream_t stream) {
+  RC_REQUIRE(flow && out, "rc_upflow8: NULL pointer");
+  RC_REQUIRE(B >= 1 && C >= 1 && (long long)B * C <= 65535 && H >= 1 && 8 * (long long)H <= 65535 && W >= 1,
+             "rc_upflow8: bad sizes B=%d C=%d H=%d W=%d", B, C, H, W);
+  return launch_upflow8(flow, B, C, H, W, out, (cudaStream_t)stream);
+}
+
+int rc_upflow8_bwd(const float *gout, int B, int C, int H, int W, float *dflow, rc_stream_t stream) {
+  RC_REQUIRE(gout && dflow, "rc_upflow8_bwd: NULL pointer");
+  RC_REQUIRE(B >= 1 && C >= 1 && (long long)B * C <= 65535 && H >= 1 && 8 * (long long)H <= 65535 && W >= 1,
+             "rc_upflow8_bwd: bad sizes B=%d C=%d H=%d W=%d", B, C, H, W);
+  return launch_upflow8_bwd(gout, B, C, H, W, dflow, (cudaStream_t)stream);
 }
 
 }  // extern "C"

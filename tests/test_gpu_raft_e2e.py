@@ -47,6 +47,24 @@ def test_flow_with_bf16_tensor_core_volume(reference_run):
     assert d <= 0.01, f"mean EPE delta {d:.5f} px > 0.01 px (mean |flow| {up.norm(dim=1).mean().item():.2f} px)"
 
 
+def test_flow_with_library_upsampling(reference_run):
+    """The fused convex upsampling (rc_upsample_flow) in place of the reference's softmax/unfold/sum: with the
+    reference's own correlation it must reproduce the flow to fp32 rounding, with this library's to the same 0.01 px."""
+    nets, im1, im2, low, up = reference_run
+    diffs = []
+
+    def both(flow, mask):          # the two upsamplings on the very same flow and mask of a real run
+        ref = Hn.upsample_flow(flow, mask)
+        diffs.append(_epe(R.upsample_flow(flow, mask), ref))
+        return ref
+
+    Hn.raft_forward(nets, im1, im2, iters=12, corr_cls=Hn.TorchCorrBlock, last_only=False, upsample_fn=both)
+    assert len(diffs) == 12 and max(diffs) <= 1e-4, f"upsampling differs from the reference's by {max(diffs):.2e} px"
+    _, got = Hn.raft_forward(nets, im1, im2, iters=12, corr_cls=R.CorrBlock, upsample_fn=R.upsample_flow)
+    d = _epe(got, up)
+    assert d <= 0.01, f"mean EPE delta {d:.5f} px > 0.01 px"
+
+
 def test_flow_with_fp32_volume(reference_run):
     nets, im1, im2, low, up = reference_run
     _, got = Hn.raft_forward(nets, im1, im2, iters=12, corr_cls=partial(R.CorrBlock, storage="fp32", math="fp32"))

@@ -120,3 +120,35 @@ def test_coords_grid_convention():
     g = O.coords_grid(2, 3, 5)
     assert g.shape == (2, 2, 3, 5)
     assert g[0, 0, 1, 4] == 4 and g[0, 1, 1, 4] == 1
+
+
+# ------------------------------------------------------------------ flow upsampling (core/raft.py:72-83, utils.py:80-82)
+@pytest.fixture(scope="module")
+def up_golden():
+    import os
+    return np.load(os.path.join(os.path.dirname(__file__), "golden", "upsample.npz"))
+
+
+@pytest.mark.parametrize("case", ["a", "b"])
+def test_upsample_oracle_matches_reference(up_golden, case):
+    from oracle import upsample_oracle as U
+    g = up_golden
+    flow, mask, gout = (g[f"{case}_{k}"].astype(np.float64) for k in ("flow", "mask", "gout"))
+    np.testing.assert_allclose(U.upsample_flow(flow, mask), g[f"{case}_up"], rtol=1e-5, atol=1e-4)
+    dflow, dmask = U.upsample_flow_backward(flow, mask, gout)
+    np.testing.assert_allclose(dflow, g[f"{case}_dflow"], rtol=1e-5, atol=1e-4)
+    np.testing.assert_allclose(dmask, g[f"{case}_dmask"], rtol=1e-5, atol=1e-4)
+    # torch derives the source position in fp32: 1e-5 relative on values of order 100
+    np.testing.assert_allclose(U.upflow8(flow), g[f"{case}_up8"], rtol=1e-5, atol=5e-4)
+    np.testing.assert_allclose(U.upflow8_backward(flow.shape, gout), g[f"{case}_dflow8"], rtol=1e-5, atol=5e-4)
+
+
+def test_upsample_is_a_convex_combination():
+    """A constant flow upsamples to 8x that constant in the interior (the weights sum to one); at the border the
+    zero padding of F.unfold pulls the result towards zero."""
+    from oracle import upsample_oracle as U
+    rng = np.random.default_rng(3)
+    flow = np.full((1, 2, 4, 5), 1.5)
+    up = U.upsample_flow(flow, rng.normal(0, 2, (1, 576, 4, 5)))
+    np.testing.assert_allclose(up[:, :, 8:-8, 8:-8], 12.0, rtol=1e-12)
+    assert (np.abs(up) <= 12.0 + 1e-9).all()
