@@ -443,6 +443,19 @@ def run_extras(R, device, args, pk):
             altv_tc = R.AlternateCorrBlock(v1, v2, LEVELS, RADIUS, math="bf16")
             out["v1080_alt_tc_lookup_ms"] = timeit(lambda: altv_tc(cv), 20)
             out["v1080_note"] = "12 iterations: default = build + 12 lookups; on-the-fly = 12 alt lookups (no volume in memory)"
+        # the step after the lookup + update block: convex 8x upsampling of the batch's flow
+        with torch.no_grad():
+            g = torch.Generator(device="cpu").manual_seed(13)
+            Bu = args.batch
+            fl = (5 * torch.randn(Bu, 2, H, W, generator=g)).to(device)
+            mk = (2 * torch.randn(Bu, 576, H, W, generator=g)).to(device)
+            ms = timeit(lambda: R.upsample_flow(fl, mk), 20)
+            up_bytes = Bu * H * W * (576 * 4 + 2 * 4 + 128 * 4)
+            out["upsample_flow_ms"] = ms
+            out["upsample_flow_GB/s"] = up_bytes / (ms * 1e-3) / 1e9
+            out["upsample_flow_frac_hbm"] = out["upsample_flow_GB/s"] / pk["hbm_gbs"]
+            out["upsample_flow_note"] = f"{Bu} maps of {H}x{W}: 2 304 B mask + 8 B flow in, 512 B out per coarse pixel"
+            del fl, mk
     except Exception as e:  # extras must never sink the headline
         out["error"] = f"{type(e).__name__}: {e}"
     return out
