@@ -12,6 +12,7 @@ import torch
 
 from . import _lib
 from ._lib import RaftCorrError, check
+from .corr import _guard
 
 
 def _check_input(t, name):
@@ -42,7 +43,7 @@ def forward(fmap1, fmap2, coords, radius):
     B, H1, W1, H2, W2, Cc, Nc = _dims(fmap1, fmap2, coords)
     rd = 2 * int(radius) + 1
     corr = torch.empty(B, Nc, rd * rd, H1, W1, dtype=torch.float32, device=fmap1.device)
-    with torch.cuda.device(fmap1.device):
+    with _guard(fmap1.device):
         check(_lib.lib().rc_alt_fwd(fmap1.data_ptr(), fmap2.data_ptr(), coords.data_ptr(), B, H1, W1, H2, W2,
                                     Cc, Nc, int(radius), corr.data_ptr(),
                                     torch.cuda.current_stream(fmap1.device).cuda_stream), "rc_alt_fwd")
@@ -58,7 +59,7 @@ def backward(fmap1, fmap2, coords, corr_grad, radius):
     g1 = torch.empty_like(fmap1)
     g2 = torch.empty_like(fmap2)
     gc = torch.empty_like(coords)
-    with torch.cuda.device(fmap1.device):
+    with _guard(fmap1.device):
         check(_lib.lib().rc_alt_bwd(fmap1.data_ptr(), fmap2.data_ptr(), coords.data_ptr(), corr_grad.data_ptr(),
                                     B, H1, W1, H2, W2, Cc, Nc, int(radius), g1.data_ptr(), g2.data_ptr(),
                                     gc.data_ptr(), torch.cuda.current_stream(fmap1.device).cuda_stream),

@@ -28,11 +28,39 @@ _MATH = {"bf16": _lib.RC_MATH_BF16, "fp32": _lib.RC_MATH_F32}
 _TORCH_DT = {_lib.RC_VOL_BF16: torch.bfloat16, _lib.RC_VOL_F32: torch.float32}
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
 def _stream(t: torch.Tensor) -> int:
+    """The current stream of the tensor's device as a raw cudaStream_t (the fast private accessor when this torch
+    has it: these wrappers run once per refinement iteration and their host time is what a single pair waits for)."""
+    if _raw_stream is not None:
+        return _raw_stream(t.device.index)
     return torch.cuda.current_stream(t.device).cuda_stream
 
 
+class _guard:
+    """`with torch.cuda.device(dev)` without its cost when dev already is the current device (the C ABI launches on
+    the current device; nn.DataParallel replicas call from threads whose current device is their own)."""
+    __slots__ = ("idx", "prev")
+
+    def __init__(self, device: torch.device):
+        self.idx = device.index
+
+    def __enter__(self):
+        self.prev = torch.cuda.current_device()
+        if self.idx is not None and self.prev != self.idx:
+            torch.cuda.set_device(self.idx)
+
+    def __exit__(self, *exc):
+        if self.idx is not None and self.prev != self.idx:
+            torch.cuda.set_device(self.prev)
+        return False
+
+
 def _require_cuda_f32(t: torch.Tensor, name: str) -> torch.Tensor:
+    if isinstance(t, torch.Tensor) and t.is_cuda and t.dtype is torch.float32 and t.is_contiguous():
+        return t
     if not isinstance(t, torch.Tensor):
         raise RaftCorrError(f"{name} must be a torch.Tensor")
     if not t.is_cuda:
@@ -133,7 +161,7 @@ class CorrBlock:
         if ws_bytes < 0:
             raise RaftCorrError("rc_build_workspace_bytes rejected the sizes")
         ws = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=self.device)
-        with torch.cuda.device(self.device):
+        with _guard(self.device):
             check(L.rc_build_pyramid(f1.data_ptr(), f2.data_ptr(), self.B, self.D, self.H, self.W,
                                      self.num_levels, self.vol_dtype, self.math, self._buf.data_ptr(),
                                      ws.data_ptr(), ws_bytes, _stream(f1)), "rc_build_pyramid")
@@ -165,7 +193,7 @@ class CorrBlock:
     def _lookup(self, coords: torch.Tensor) -> torch.Tensor:
         n = 2 * self.radius + 1
         out = torch.empty(self.B, self.num_levels * n * n, self.H, self.W, dtype=torch.float32, device=self.device)
-        with torch.cuda.device(self.device):
+        with _guard(self.device):
             check(_lib.lib().rc_lookup_fwd(self._buf.data_ptr(), self.vol_dtype, coords.data_ptr(), self.B,
                                            self.H, self.W, self.num_levels, self.radius, out.data_ptr(),
                                            _stream(coords)), "rc_lookup_fwd")
@@ -186,7 +214,7 @@ class CorrBlock:
         dcoords = torch.empty_like(coords) if want_coords else None
         if not (want_vol or want_coords):
             return None
-        with torch.cuda.device(self.device):
+        with _guard(self.device):
             check(L.rc_lookup_bwd(self._buf.data_ptr(), self.vol_dtype, coords.data_ptr(), grad_out.data_ptr(),
                                   self.B, self.H, self.W, self.num_levels, self.radius,
                                   self._grad_buf.data_ptr() if want_vol else None,
@@ -202,7 +230,7 @@ class CorrBlock:
         L = _lib.lib()
         ws_bytes = int(L.rc_build_bwd_workspace_bytes(self.B, self.D, self.H, self.W, self.num_levels))
         ws = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=self.device)
-        with torch.cuda.device(self.device):
+        with _guard(self.device):
             check(L.rc_build_bwd(self._grad_buf.data_ptr(), f1.data_ptr(), f2.data_ptr(), self.B, self.D,
                                  self.H, self.W, self.num_levels, d1.data_ptr(), d2.data_ptr(),
                                  ws.data_ptr(), ws_bytes, _stream(f1)), "rc_build_bwd")
@@ -242,7 +270,7 @@ class AlternateCorrBlock:
         self._offs = [int(offs[l]) for l in range(num_levels)]
         self._f1 = torch.empty(self.B, self.H, self.W, self.D, dtype=torch.float32, device=self.device)
         self._f2 = torch.empty(total, dtype=torch.float32, device=self.device)
-        with torch.cuda.device(self.device):
+        with _guard(self.device):
             check(L.rc_alt_pool_features(f1.data_ptr(), f2.data_ptr(), self.B, self.D, self.H, self.W,
                                          num_levels, self._f1.data_ptr(), self._f2.data_ptr(), _stream(f1)),
                   "rc_alt_pool_features")
@@ -251,7 +279,7 @@ class AlternateCorrBlock:
                 raise RaftCorrError(f"math='bf16' needs D % 64 == 0 (got D={self.D})")
             self._f1h = torch.empty(self.B, self.H, self.W, self.D, dtype=torch.bfloat16, device=self.device)
             self._f2h = torch.empty(total, dtype=torch.bfloat16, device=self.device)
-            with torch.cuda.device(self.device):
+            with _guard(self.device):
                 check(L.rc_alt_features_bf16(self._f1.data_ptr(), self._f2.data_ptr(), self.B, self.D, self.H,
                                              self.W, num_levels, self._f1h.data_ptr(), self._f2h.data_ptr(),
                                              _stream(f1)), "rc_alt_features_bf16")
@@ -268,7 +296,7 @@ class AlternateCorrBlock:
             raise RaftCorrError(f"coords shape {tuple(c.shape)}, expected {(self.B, 2, self.H, self.W)}")
         n = 2 * self.radius + 1
         out = torch.empty(self.B, self.num_levels * n * n, self.H, self.W, dtype=torch.float32, device=self.device)
-        with torch.cuda.device(self.device):
+        with _guard(self.device):
             if self.math == "bf16":
                 check(_lib.lib().rc_alt_lookup_fwd_tc(self._f1h.data_ptr(), self._f2h.data_ptr(), c.data_ptr(), self.B,
                                                       self.D, self.H, self.W, self.num_levels, self.radius,

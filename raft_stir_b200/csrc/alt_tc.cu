@@ -744,12 +744,29 @@ int launch_alt_lookup_tc(const void *f1_bf16, const void *f2_pyr_bf16, const flo
   int r;
   if (D <= P_MAX_KB * KB) {
     // persistent kernel: query features resident, fmap2 in boxes of two target rows (32 or 16 targets wide)
-    PersistMaps maps;
-    if ((r = encode_nhwc(&maps.f1, f1_bf16, B, D, H, W, QB_W, QB_H))) return r;
-    for (int l = 0; l < RC_MAX_LEVELS; ++l) {
-      if ((r = encode_nhwc(&maps.f2w[l], level(l), B, D, p.Hl[l], p.Wl[l], CH_W, 2))) return r;
-      if ((r = encode_nhwc(&maps.f2n[l], level(l), B, D, p.Hl[l], p.Wl[l], HALF_W, 2))) return r;
+    // The nine descriptors depend only on the buffers and the shape: a block is looked up once per refinement
+    // iteration with the same ones, so the last few sets are kept per host thread (descriptors are plain data
+    // holding addresses: a stale entry can only be hit by a call that passes the very same buffers and shape).
+    struct Cached { const void *f1, *f2; int B, D, H, W, L; PersistMaps maps; };
+    thread_local Cached cache[4];
+    thread_local int next = 0;
+    const PersistMaps *mp = nullptr;
+    for (const Cached &c : cache)
+      if (c.f1 == f1_bf16 && c.f2 == f2_pyr_bf16 && c.B == B && c.D == D && c.H == H && c.W == W && c.L == num_levels)
+        mp = &c.maps;
+    if (!mp) {
+      Cached &c = cache[next];
+      c.f1 = nullptr;                                     // invalid while being rewritten
+      if ((r = encode_nhwc(&c.maps.f1, f1_bf16, B, D, H, W, QB_W, QB_H))) return r;
+      for (int l = 0; l < RC_MAX_LEVELS; ++l) {
+        if ((r = encode_nhwc(&c.maps.f2w[l], level(l), B, D, p.Hl[l], p.Wl[l], CH_W, 2))) return r;
+        if ((r = encode_nhwc(&c.maps.f2n[l], level(l), B, D, p.Hl[l], p.Wl[l], HALF_W, 2))) return r;
+      }
+      c.f1 = f1_bf16; c.f2 = f2_pyr_bf16; c.B = B; c.D = D; c.H = H; c.W = W; c.L = num_levels;
+      next = (next + 1) % 4;
+      mp = &c.maps;
     }
+    const PersistMaps &maps = *mp;
     switch (radius) {
       case 1: return alt_tc_launch_persistent<1>(maps, coords, out, p, s);
       case 2: return alt_tc_launch_persistent<2>(maps, coords, out, p, s);

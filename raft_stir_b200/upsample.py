@@ -19,19 +19,23 @@ import torch
 
 from . import _lib
 from ._lib import RaftCorrError, check
-from .corr import _require_cuda_f32, _stream
+from .corr import _guard, _require_cuda_f32, _stream
+
+
+def _upsample_fwd(flow, mask):
+    B, _, H, W = flow.shape
+    out = torch.empty(B, 2, 8 * H, 8 * W, device=flow.device, dtype=torch.float32)
+    with _guard(flow.device):
+        check(_lib.lib().rc_upsample_flow(flow.data_ptr(), mask.data_ptr(), B, H, W, out.data_ptr(), _stream(flow)),
+              "rc_upsample_flow")
+    return out
 
 
 class _UpsampleFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, flow, mask):
-        B, _, H, W = flow.shape
-        out = torch.empty(B, 2, 8 * H, 8 * W, device=flow.device, dtype=torch.float32)
-        with torch.cuda.device(flow.device):
-            check(_lib.lib().rc_upsample_flow(flow.data_ptr(), mask.data_ptr(), B, H, W, out.data_ptr(), _stream(flow)),
-                  "rc_upsample_flow")
         ctx.save_for_backward(flow, mask)
-        return out
+        return _upsample_fwd(flow, mask)
 
     @staticmethod
     def backward(ctx, gout):
@@ -40,7 +44,7 @@ class _UpsampleFn(torch.autograd.Function):
         gout = gout.contiguous().float()
         dflow = torch.empty_like(flow)
         dmask = torch.empty_like(mask)
-        with torch.cuda.device(flow.device):
+        with _guard(flow.device):
             check(_lib.lib().rc_upsample_flow_bwd(flow.data_ptr(), mask.data_ptr(), gout.data_ptr(), B, H, W,
                                                   dflow.data_ptr(), dmask.data_ptr(), _stream(flow)),
                   "rc_upsample_flow_bwd")
@@ -52,7 +56,7 @@ class _Upflow8Fn(torch.autograd.Function):
     def forward(ctx, flow):
         B, Cn, H, W = flow.shape
         out = torch.empty(B, Cn, 8 * H, 8 * W, device=flow.device, dtype=torch.float32)
-        with torch.cuda.device(flow.device):
+        with _guard(flow.device):
             check(_lib.lib().rc_upflow8(flow.data_ptr(), B, Cn, H, W, out.data_ptr(), _stream(flow)), "rc_upflow8")
         ctx.shape = (B, Cn, H, W)
         return out
@@ -62,7 +66,7 @@ class _Upflow8Fn(torch.autograd.Function):
         B, Cn, H, W = ctx.shape
         gout = gout.contiguous().float()
         dflow = torch.empty(B, Cn, H, W, device=gout.device, dtype=torch.float32)
-        with torch.cuda.device(gout.device):
+        with _guard(gout.device):
             check(_lib.lib().rc_upflow8_bwd(gout.data_ptr(), B, Cn, H, W, dflow.data_ptr(), _stream(gout)),
                   "rc_upflow8_bwd")
         return dflow
@@ -78,7 +82,9 @@ def upsample_flow(flow: torch.Tensor, mask: torch.Tensor) -> torch.Tensor:
         raise RaftCorrError(f"flow must be [B,2,H,W], got {tuple(flow.shape)}")
     if mask.dim() != 4 or mask.shape[1] != 576 or mask.shape[0] != flow.shape[0] or mask.shape[2:] != flow.shape[2:]:
         raise RaftCorrError(f"mask must be [B,576,H,W] matching flow {tuple(flow.shape)}, got {tuple(mask.shape)}")
-    return _UpsampleFn.apply(flow, mask)
+    if torch.is_grad_enabled() and (flow.requires_grad or mask.requires_grad):
+        return _UpsampleFn.apply(flow, mask)
+    return _upsample_fwd(flow, mask)          # inference: no autograd node to build
 
 
 def upflow8(flow: torch.Tensor, mode: str = "bilinear") -> torch.Tensor:
