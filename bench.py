@@ -447,6 +447,21 @@ def run_extras(R, device, args, pk):
             altv_tc = R.AlternateCorrBlock(v1, v2, LEVELS, RADIUS, math="bf16")
             out["v1080_alt_tc_lookup_ms"] = timeit(lambda: altv_tc(cv), 20)
             out["v1080_note"] = "12 iterations: default = build + 12 lookups; on-the-fly = 12 alt lookups (no volume in memory)"
+        # the headline's lookup with fp16 output (what an update block under fp16 autocast consumes), same batch
+        with torch.no_grad():
+            f1b = torch.randn(args.batch, D, H, W, device=device)
+            f2b = torch.randn(args.batch, D, H, W, device=device)
+            cb = R.coords_grid(args.batch, H, W, device) + 5 * torch.randn(args.batch, 2, H, W, device=device)
+            blk16 = R.CorrBlock(f1b, f2b, LEVELS, RADIUS, storage=args.storage, out_dtype=torch.float16)
+            del f1b, f2b
+            ms = timeit(lambda: blk16(cb), 20)
+            nq = args.batch * H * W
+            b16 = nq * (LEVELS * (2 * RADIUS + 2) ** 2 * (2 if args.storage == "bf16" else 4) + 8
+                        + LEVELS * (2 * RADIUS + 1) ** 2 * 2)
+            out["lookup_fp16_out_ms"] = ms
+            out["lookup_fp16_out_GB/s"] = b16 / (ms * 1e-3) / 1e9
+            out["lookup_fp16_out_frac_hbm"] = out["lookup_fp16_out_GB/s"] / pk["hbm_gbs"]
+            del blk16, cb
         # the step after the lookup + update block: convex 8x upsampling of the batch's flow
         with torch.no_grad():
             g = torch.Generator(device="cpu").manual_seed(13)

@@ -144,6 +144,14 @@ RC_API int rc_build_pyramid_static(const float *fmap1, const float *fmap2, int B
  */
 RC_API int rc_lookup_fwd(const void *pyramid, int vol_dtype, const float *coords, int B, int H, int W,
                   int num_levels, int radius, float *out, rc_stream_t stream);
+/*
+ * The same lookup with the result rounded once to IEEE half precision: out_f16 is fp16 [B, num_levels*(2r+1)^2, H, W].
+ * For callers whose next op runs under fp16 autocast (the update block, core/raft.py:127-128, with
+ * --mixed_precision): the reference hands over fp32 and autocast's first convolution casts it; here the cast pass
+ * and half of the lookup's output bytes disappear.  No counterpart in the reference; inference only.
+ */
+RC_API int rc_lookup_fwd_f16(const void *pyramid, int vol_dtype, const float *coords, int B, int H, int W,
+                      int num_levels, int radius, void *out_f16, rc_stream_t stream);
 
 /*
  * Backward of rc_lookup_fwd: what autograd of F.grid_sample yields at

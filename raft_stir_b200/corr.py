@@ -119,13 +119,21 @@ class CorrBlock:
     storage: "bf16" (default) or "fp32" -- element type of the stored pyramid.
     math:    "bf16" (default; tcgen05 tensor cores, fp32 accumulate) or "fp32"
              (CUDA-core fp32 FMA, the reference's SGEMM arithmetic).
-    Defaults can be set with RAFT_CORR_STORAGE / RAFT_CORR_MATH.
+    out_dtype: torch.float32 (default, the reference's) or torch.float16 -- element type of what the call returns.
+             fp16 is for inference under fp16 autocast (--mixed_precision): the update block's first convolution
+             would cast the fp32 result itself; the lookup then writes half the bytes and the cast pass disappears.
+    Defaults can be set with RAFT_CORR_STORAGE / RAFT_CORR_MATH / RAFT_CORR_OUT (fp32|fp16).
     """
 
     def __init__(self, fmap1, fmap2, num_levels: int = 4, radius: int = 4, *,
-                 storage: Optional[str] = None, math: Optional[str] = None):
+                 storage: Optional[str] = None, math: Optional[str] = None, out_dtype: Optional[torch.dtype] = None):
         self.num_levels = num_levels
         self.radius = radius
+        if out_dtype is None:
+            out_dtype = {"fp32": torch.float32, "fp16": torch.float16}.get(os.environ.get("RAFT_CORR_OUT", "fp32"))
+        if out_dtype not in (torch.float32, torch.float16):
+            raise RaftCorrError(f"out_dtype={out_dtype!r}: expected torch.float32 or torch.float16")
+        self.out_dtype = out_dtype
         storage = storage or os.environ.get("RAFT_CORR_STORAGE", "bf16")
         math = math or os.environ.get("RAFT_CORR_MATH", "bf16")
         if storage not in _STORAGE or math not in _MATH:
@@ -190,20 +198,20 @@ class CorrBlock:
             raise RaftCorrError("coords must be on the pyramid's device")
         return c
 
-    def _lookup(self, coords: torch.Tensor) -> torch.Tensor:
+    def _lookup(self, coords: torch.Tensor, out_dtype: torch.dtype = torch.float32) -> torch.Tensor:
         n = 2 * self.radius + 1
-        out = torch.empty(self.B, self.num_levels * n * n, self.H, self.W, dtype=torch.float32, device=self.device)
+        out = torch.empty(self.B, self.num_levels * n * n, self.H, self.W, dtype=out_dtype, device=self.device)
+        fn = _lib.lib().rc_lookup_fwd if out_dtype is torch.float32 else _lib.lib().rc_lookup_fwd_f16
         with _guard(self.device):
-            check(_lib.lib().rc_lookup_fwd(self._buf.data_ptr(), self.vol_dtype, coords.data_ptr(), self.B,
-                                           self.H, self.W, self.num_levels, self.radius, out.data_ptr(),
-                                           _stream(coords)), "rc_lookup_fwd")
+            check(fn(self._buf.data_ptr(), self.vol_dtype, coords.data_ptr(), self.B, self.H, self.W,
+                     self.num_levels, self.radius, out.data_ptr(), _stream(coords)), "rc_lookup_fwd")
         return out
 
     def __call__(self, coords: torch.Tensor) -> torch.Tensor:
         c = self._check_coords(coords)
         if torch.is_grad_enabled() and (self._token is not None or c.requires_grad):
-            return _LookupFn.apply(c, self._token, self)
-        return self._lookup(c)
+            return _LookupFn.apply(c, self._token, self)      # training: fp32, as the reference
+        return self._lookup(c, self.out_dtype)
 
     # --------------------------------------------------------------- backward
     def _lookup_backward(self, coords, grad_out, want_vol: bool, want_coords: bool):

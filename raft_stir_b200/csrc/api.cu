@@ -188,6 +188,16 @@ int rc_lookup_fwd(const void *pyramid, int vol_dtype, const float *coords, int B
   return launch_lookup_fwd(pyramid, vol_dtype, coords, lay, H, W, radius, out, (cudaStream_t)stream);
 }
 
+int rc_lookup_fwd_f16(const void *pyramid, int vol_dtype, const float *coords, int B, int H, int W, int num_levels,
+                      int radius, void *out_f16, rc_stream_t stream) {
+  RC_REQUIRE(pyramid && coords && out_f16, "rc_lookup_fwd_f16: NULL pointer");
+  RC_REQUIRE(radius >= 1 && radius <= 4, "radius %d unsupported (1..4)", radius);
+  rc_layout lay;
+  int r = make_layout(B, H, W, num_levels, vol_dtype, &lay);
+  if (r) return r;
+  return launch_lookup_fwd_f16(pyramid, vol_dtype, coords, lay, radius, out_f16, (cudaStream_t)stream);
+}
+
 int rc_lookup_bwd(const void *pyramid, int vol_dtype, const float *coords, const float *grad_out, int B,
                   int H, int W, int num_levels, int radius, float *grad_pyramid, float *grad_coords,
                   rc_stream_t stream) {

@@ -122,6 +122,8 @@ int launch_pool_levels(const rc_layout &lay, int vol_dtype, void *pyramid, int f
 int launch_build_tc(const void *f1p, const void *f2p, int B, int D, int H, int W,
                     const rc_layout &lay, int vol_dtype, int math, void *pyramid, cudaStream_t s);
 // lookup.cu
+int launch_lookup_fwd_f16(const void *pyramid, int vol_dtype, const float *coords, const rc_layout &lay, int radius,
+                          void *out_f16, cudaStream_t s);
 int launch_lookup_fwd(const void *pyramid, int vol_dtype, const float *coords, const rc_layout &lay,
                       int H, int W, int radius, float *out, cudaStream_t s);
 int launch_lookup_bwd(const void *pyramid, int vol_dtype, const float *coords, const float *grad_out,

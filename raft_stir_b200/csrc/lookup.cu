@@ -30,6 +30,7 @@
 // materialises the sampling grid, four per-level outputs, a cat and a
 // permute().contiguous() copy).
 #include "common.cuh"
+#include <cuda_fp16.h>
 
 namespace rc {
 namespace {
@@ -222,10 +223,19 @@ __device__ __forceinline__ void read_row(uint32_t win, int lane, int j, int o, u
 }
 
 // grid: B * ceil(N/32) strips; block: 32 * num_levels threads; dyn smem: L * WIN_BYTES
-template <typename VolT, int R>
+template <typename OutT>
+__device__ __forceinline__ OutT to_out(float v);
+template <>
+__device__ __forceinline__ float to_out<float>(float v) { return v; }
+template <>
+__device__ __forceinline__ __half to_out<__half>(float v) { return __float2half_rn(v); }
+
+// OutT = float: the reference's output.  OutT = __half: the same values rounded once to fp16, for callers whose
+// next op runs under fp16 autocast (core/raft.py:127-128) and would cast the fp32 output itself.
+template <typename VolT, int R, typename OutT>
 __global__ void __launch_bounds__(32 * RC_MAX_LEVELS)
 lookup_fwd_kernel(const VolT *__restrict__ pyr, const float *__restrict__ coords,
-                  float *__restrict__ out, Levels lv, int N, int strips_per_pair) {
+                  OutT *__restrict__ out, Levels lv, int N, int strips_per_pair) {
   using W_ = Win<VolT, R>;
   extern __shared__ __align__(16) uint32_t smem_u[];
   const int lane = threadIdx.x & 31;
@@ -256,7 +266,7 @@ lookup_fwd_kernel(const VolT *__restrict__ pyr, const float *__restrict__ coords
   if (!active) return;
   const int o = w.x0 & (W_::EPV - 1);
   const int C = lv.num_levels * W_::NW * W_::NW;
-  float *op = out + ((size_t)b * C + (size_t)l * W_::NW * W_::NW) * N + q;
+  OutT *op = out + ((size_t)b * C + (size_t)l * W_::NW * W_::NW) * N + q;
   float hprev[W_::NW];
 #pragma unroll
   for (int j = 0; j < W_::T; ++j) {
@@ -267,7 +277,7 @@ lookup_fwd_kernel(const VolT *__restrict__ pyr, const float *__restrict__ coords
     if (j > 0) {
 #pragma unroll
       for (int i = 0; i < W_::NW; ++i)
-        op[(size_t)(i * W_::NW + (j - 1)) * N] = fmaf(w.ay, h[i] - hprev[i], hprev[i]);
+        op[(size_t)(i * W_::NW + (j - 1)) * N] = to_out<OutT>(fmaf(w.ay, h[i] - hprev[i], hprev[i]));
     }
 #pragma unroll
     for (int i = 0; i < W_::NW; ++i) hprev[i] = h[i];
@@ -455,14 +465,14 @@ lookup_bwd_kernel(const VolT *__restrict__ pyr, const float *__restrict__ coords
   }
 }
 
-template <typename VolT, int R>
-int lookup_fwd_t(const VolT *pyr, const float *coords, const rc_layout &lay, float *out,
+template <typename VolT, int R, typename OutT>
+int lookup_fwd_t(const VolT *pyr, const float *coords, const rc_layout &lay, OutT *out,
                  cudaStream_t s) {
   using W_ = Win<VolT, R>;
   const int N = lay.N;
   const int strips = ceil_div(N, 32);
   const size_t smem = (size_t)lay.num_levels * W_::WIN_BYTES;
-  auto kern = lookup_fwd_kernel<VolT, R>;
+  auto kern = lookup_fwd_kernel<VolT, R, OutT>;
   RC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   kern<<<lay.B * strips, 32 * lay.num_levels, smem, s>>>(pyr, coords, out, to_levels(lay), N, strips);
   RC_LAUNCH_CHECK("lookup_fwd_kernel");
@@ -497,13 +507,32 @@ int lookup_bwd_t(const VolT *pyr, const float *coords, const float *grad_out, co
     default: set_error("radius %d unsupported (1..4)", radius); return RC_EINVAL; \
   }
 
+#define RC_DISPATCH_R2(FN, VT, OT, ...)                             \
+  switch (radius) {                                                 \
+    case 1: return FN<VT, 1, OT>(__VA_ARGS__);                      \
+    case 2: return FN<VT, 2, OT>(__VA_ARGS__);                      \
+    case 3: return FN<VT, 3, OT>(__VA_ARGS__);                      \
+    case 4: return FN<VT, 4, OT>(__VA_ARGS__);                      \
+    default: set_error("radius %d unsupported (1..4)", radius); return RC_EINVAL; \
+  }
+
 int launch_lookup_fwd(const void *pyramid, int vol_dtype, const float *coords, const rc_layout &lay,
                       int H, int W, int radius, float *out, cudaStream_t s) {
   (void)H; (void)W;
   if (vol_dtype == RC_VOL_BF16) {
-    RC_DISPATCH_R(lookup_fwd_t, __nv_bfloat16, (const __nv_bfloat16 *)pyramid, coords, lay, out, s)
+    RC_DISPATCH_R2(lookup_fwd_t, __nv_bfloat16, float, (const __nv_bfloat16 *)pyramid, coords, lay, out, s)
   } else {
-    RC_DISPATCH_R(lookup_fwd_t, float, (const float *)pyramid, coords, lay, out, s)
+    RC_DISPATCH_R2(lookup_fwd_t, float, float, (const float *)pyramid, coords, lay, out, s)
+  }
+}
+
+int launch_lookup_fwd_f16(const void *pyramid, int vol_dtype, const float *coords, const rc_layout &lay, int radius,
+                          void *out_f16, cudaStream_t s) {
+  __half *out = (__half *)out_f16;
+  if (vol_dtype == RC_VOL_BF16) {
+    RC_DISPATCH_R2(lookup_fwd_t, __nv_bfloat16, __half, (const __nv_bfloat16 *)pyramid, coords, lay, out, s)
+  } else {
+    RC_DISPATCH_R2(lookup_fwd_t, float, __half, (const float *)pyramid, coords, lay, out, s)
   }
 }
 

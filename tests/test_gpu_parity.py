@@ -176,6 +176,29 @@ def test_lookup_isolated_from_build(radius, storage):
     rel_close(out, O.window_lookup(pyr, coords, radius), 2e-5, f"isolated lookup r={radius} {storage}")
 
 
+@pytest.mark.parametrize("radius", [3, 4])
+@pytest.mark.parametrize("storage", ["bf16", "fp32"])
+def test_lookup_fp16_output_is_the_fp32_output_rounded_once(radius, storage):
+    """rc_lookup_fwd_f16 (CorrBlock(out_dtype=torch.float16)): bit-identical to the fp32 result cast to fp16 by torch,
+    i.e. exactly what fp16 autocast would make of the reference's output; training calls still return fp32."""
+    B, D, H, W = 2, 32, 19, 45
+    rng = np.random.default_rng(radius + len(storage))
+    f1, f2 = (t(rng.standard_normal((B, D, H, W)).astype(np.float32)) for _ in range(2))
+    coords = t((O.coords_grid(B, H, W) + rng.normal(0, 4, (B, 2, H, W))).astype(np.float32))
+    math = "fp32" if storage == "fp32" else "bf16"
+    ref = R.CorrBlock(f1, f2, 4, radius, storage=storage, math=math)(coords)
+    blk = R.CorrBlock(f1, f2, 4, radius, storage=storage, math=math, out_dtype=torch.float16)
+    with torch.no_grad():
+        got = blk(coords)
+    assert got.dtype == torch.float16 and got.is_contiguous() and got.shape == ref.shape
+    assert torch.equal(got, ref.half())
+    # with autograd in play the block answers in fp32 like the reference
+    cg = coords.clone().requires_grad_(True)
+    assert blk(cg).dtype == torch.float32
+    with pytest.raises(RuntimeError):
+        R.CorrBlock(f1, f2, 4, radius, out_dtype=torch.bfloat16)
+
+
 def test_lookup_far_and_nonfinite_coords_are_zero():
     B, H, W = 1, 16, 24
     rng = np.random.default_rng(0)
