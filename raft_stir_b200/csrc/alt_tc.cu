@@ -363,29 +363,41 @@ alt_tc_persist_kernel(const __grid_constant__ PersistMaps maps, const float *__r
   if (warp == 0) {
     // ===================================================== scout + TMA producer
     uint32_t st = 0, ph = 0, dcount = 0, nu = 0;
+    // this lane's share of a block: queries 4*lane .. 4*lane+3 (a quarter of one block row); their coordinates
+    // are fetched one unit ahead so that the first box of a unit is known the moment the previous unit is issued
+    float cxn[4], cyn[4];
+    bool insn[4];
+    auto fetch = [&](int u) {
+      if (u >= pp.n_units) return;
+      const int item = u % pp.n_items;
+      const int b = item / nblk, blk = item - b * nblk;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int ql = lane * 4 + k;
+        const int yq = (blk / p.nbx) * QB_H + ql / QB_W, xq = (blk % p.nbx) * QB_W + ql % QB_W;
+        insn[k] = yq < p.H && xq < p.W;
+        const int q = insn[k] ? yq * p.W + xq : 0;
+        cxn[k] = __ldg(coords + ((size_t)b * 2 + 0) * N1 + q);
+        cyn[k] = __ldg(coords + ((size_t)b * 2 + 1) * N1 + q);
+      }
+    };
+    fetch(blockIdx.x);
     for (int u = blockIdx.x; u < pp.n_units; u += gridDim.x, ++nu) {
       const int lg = u / pp.n_items, item = u - lg * pp.n_items;      // fine levels (most chunks) first
       const int b = item / nblk, blk = item - b * nblk;
       const int qy0 = (blk / p.nbx) * QB_H, qx0 = (blk % p.nbx) * QB_W;
       const int l_begin = lg * pp.lpu, l_end = min(p.num_levels, l_begin + pp.lpu);
+      float cxs[4], cys[4];
+      bool inside[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) { cxs[k] = cxn[k]; cys[k] = cyn[k]; inside[k] = insn[k]; }
+      fetch(u + gridDim.x);
       if (lane == 0) {
         for (int kb = 0; kb < NKB; ++kb) {
           mbar_wait(a_empty + 8 * kb, (nu & 1) ^ 1);
           mbar_expect_tx(a_full + 8 * kb, A_BYTES);
           tma_load_4d(sA + kb * A_BYTES, &maps.f1, a_full + 8 * kb, kb * KB, qx0, qy0, b);
         }
-      }
-      // this lane's share of the block: queries 4*lane .. 4*lane+3 (a quarter of one block row)
-      float cxs[4], cys[4];
-      bool inside[4];
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const int ql = lane * 4 + k;
-        const int yq = qy0 + ql / QB_W, xq = qx0 + ql % QB_W;
-        inside[k] = yq < p.H && xq < p.W;
-        const int q = inside[k] ? yq * p.W + xq : 0;
-        cxs[k] = __ldg(coords + ((size_t)b * 2 + 0) * N1 + q);
-        cys[k] = __ldg(coords + ((size_t)b * 2 + 1) * N1 + q);
       }
       for (int l = l_begin; l < l_end; ++l) {
         const int Hl = p.Hl[l], Wl = p.Wl[l];
