@@ -21,13 +21,15 @@ from oracle import raft_harness as Hn   # noqa: E402
 
 
 class Net(nn.Module):
-    def __init__(self, nets, corr_cls):
+    def __init__(self, nets, corr_cls, upsample_fn=None):
         super().__init__()
         self.fnet, self.cnet, self.update = nets
         self.corr_cls = corr_cls
+        self.upsample_fn = upsample_fn
 
     def forward(self, im1, im2):
-        return Hn.raft_forward_train((self.fnet, self.cnet, self.update), im1, im2, 12, self.corr_cls)
+        return Hn.raft_forward_train((self.fnet, self.cnet, self.update), im1, im2, 12, self.corr_cls,
+                                     upsample_fn=self.upsample_fn)
 
 
 def main():
@@ -47,8 +49,9 @@ def main():
     gt = (5 * torch.randn(B, 2, H, W, generator=g)).to(dev)
     valid = torch.ones(B, H, W, device=dev)
     res = {"config": f"RAFT-basic train step, {B} pairs/GPU 368x496, 12 iters, fp32, {world} GPU(s)"}
-    for name, cls in (("torch_corrblock", Hn.TorchCorrBlock), ("ours_bf16", R.CorrBlock)):
-        model = Net(Hn.load(dev), cls).to(dev)
+    for name, cls, ups in (("torch_corrblock", Hn.TorchCorrBlock, None), ("ours_bf16", R.CorrBlock, None),
+                           ("ours_bf16_and_upsampling", R.CorrBlock, R.upsample_flow)):
+        model = Net(Hn.load(dev), cls, ups).to(dev)
         if world > 1:
             model = nn.parallel.DistributedDataParallel(model, device_ids=[local])
         opt = torch.optim.AdamW(model.parameters(), lr=1e-5, weight_decay=1e-4)
@@ -61,7 +64,7 @@ def main():
             opt.step()
             return loss
 
-        for _ in range(2):
+        for _ in range(3):
             step()
         torch.cuda.synchronize()
         if dist is not None:
