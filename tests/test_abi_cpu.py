@@ -99,3 +99,24 @@ def test_level_view_inverts_the_tile_layout():
                 want = (lay.offset[l] + q * lay.slab[l] + ((y // th) * lay.tiles_x[l] + x // tw) * th * tw
                         + (y % th) * tw + x % tw)
                 assert int(v[q, y, x]) == want
+
+
+def test_install_into_rebinds_the_reference_names():
+    """install_into swaps the names core/raft.py:8 imports and (unless told not to) the two upsampling functions
+    (core/raft.py:72-83, core/utils/utils.py:80-82 as imported into core/raft.py)."""
+    import types
+
+    import raft_stir_b200 as R
+
+    class FakeRAFT:
+        def upsample_flow(self, flow, mask):
+            return "reference"
+
+    mod = types.SimpleNamespace(CorrBlock=object, AlternateCorrBlock=object, RAFT=FakeRAFT, upflow8=lambda f: "reference")
+    R.install_into(mod, upsampling=False)
+    assert mod.CorrBlock is R.CorrBlock and mod.AlternateCorrBlock is R.AlternateCorrBlock
+    assert FakeRAFT().upsample_flow(None, None) == "reference" and mod.upflow8(None) == "reference"
+    R.install_into(mod)
+    assert mod.upflow8 is R.upflow8
+    with __import__("pytest").raises(RuntimeError):          # now routed to the library, which rejects CPU tensors
+        FakeRAFT().upsample_flow(__import__("torch").zeros(1, 2, 4, 4), __import__("torch").zeros(1, 576, 4, 4))
