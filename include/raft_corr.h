@@ -44,7 +44,7 @@ extern "C" {
 /* arithmetic used to form the feature dot products of the volume build */
 #define RC_MATH_F32 0    /* CUDA-core fp32 FMA: what the reference's SGEMM does */
 #define RC_MATH_BF16 1   /* tcgen05 kind::f16, bf16 operands, fp32 accumulate in TMEM */
-#define RC_MATH_TF32 2   /* tcgen05 kind::tf32, fp32 operands read as tf32 */
+#define RC_MATH_TF32 2   /* reserved (tcgen05 kind::tf32); not implemented: rc_build_pyramid returns RC_EINVAL */
 
 typedef struct CUstream_st *rc_stream_t;   /* == cudaStream_t */
 
