@@ -29,6 +29,7 @@
 #include <cuda.h>
 
 #include "common.cuh"
+#include "tc_ptx.cuh"
 
 namespace rc {
 namespace {
@@ -96,108 +97,9 @@ struct TileWalk {
   __device__ __forceinline__ bool a_changes(int cb, int cm) const { return left == 0 || b != cb || m != cm; }
 };
 
-// ---------------------------------------------------------------- PTX wrappers
-__device__ __forceinline__ uint32_t smem_u32(const void *p) {
-  return (uint32_t)__cvta_generic_to_shared(p);
-}
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ bool mbar_try(uint32_t bar, uint32_t parity) {
-  uint32_t ok;
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-      "selp.u32 %0, 1, 0, p;\n\t}"
-      : "=r"(ok)
-      : "r"(bar), "r"(parity)
-      : "memory");
-  return ok != 0;
-}
-// Slow path of a wait, bounded: a protocol bug must surface as a launch error,
-// never as a hung GPU.
-__device__ __noinline__ void mbar_wait_slow(uint32_t bar, uint32_t parity) {
-  unsigned long long t0 = 0;
-  for (uint32_t spin = 1;; ++spin) {
-    if (mbar_try(bar, parity)) return;
-    if ((spin & 0xff) == 0) {
-      unsigned long long now;
-      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
-      if (t0 == 0) t0 = now;
-      else if (now - t0 > 2000000000ull) __trap();   // 2 s
-    }
-  }
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  if (!mbar_try(bar, parity)) mbar_wait_slow(bar, parity);
-}
-// L2 eviction policies: the packed operands are re-read by every CTA (keep them),
-// the volume is written once and not read by this kernel (let it go first).
-__device__ __forceinline__ uint64_t l2_policy_evict_last() {
-  uint64_t pol;
-  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
-  return pol;
-}
-__device__ __forceinline__ uint64_t l2_policy_evict_first() {
-  uint64_t pol;
-  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
-  return pol;
-}
-__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0,
-                                            int c1, int c2, uint64_t policy) {
-  asm volatile(
-      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
-      " [%0], [%1, {%3, %4, %5}], [%2], %6;"
-      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "l"(policy)
-      : "memory");
-}
-__device__ __forceinline__ void stg16_hint(void *dst, const uint4 &v, uint64_t policy) {
-  asm volatile("st.global.L2::cache_hint.v4.b32 [%0], {%1, %2, %3, %4}, %5;" ::"l"(dst), "r"(v.x), "r"(v.y), "r"(v.z),
-               "r"(v.w), "l"(policy)
-               : "memory");
-}
-__device__ __forceinline__ void stg8_hint(void *dst, uint32_t a, uint32_t b, uint64_t policy) {
-  asm volatile("st.global.L2::cache_hint.v2.b32 [%0], {%1, %2}, %3;" ::"l"(dst), "r"(a), "r"(b), "l"(policy) : "memory");
-}
-__device__ __forceinline__ void stg4_hint(void *dst, uint32_t a, uint64_t policy) {
-  asm volatile("st.global.L2::cache_hint.b32 [%0], %1, %2;" ::"l"(dst), "r"(a), "l"(policy) : "memory");
-}
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
-                                          uint32_t accumulate) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-      : "memory");
-}
-// 32 TMEM lanes x 16 consecutive columns -> 16 registers per thread (lane = this thread's query)
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t *r) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-      : "r"(taddr));
-}
-__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// PTX wrappers (mbarrier, TMA, tcgen05, L2 policies): tc_ptx.cuh
+using namespace tc;
 
-// K-major, 128-byte-swizzled operand tile: rows of 128 bytes, 8-row groups 1024 bytes apart.
-// hi word: SBO = 1024 B, version 1, SWIZZLE_128B;  lo word: start address >> 4, LBO = 1 (unused).
-constexpr uint32_t DESC_HI = (1024u >> 4) | (1u << 14) | (2u << 29);
-__device__ __forceinline__ uint32_t desc_lo(uint32_t saddr) { return ((saddr >> 4) & 0x3fffu) | (1u << 16); }
-__device__ __forceinline__ uint64_t desc_make(uint32_t lo) { return ((uint64_t)DESC_HI << 32) | lo; }
 // kind::f16: D = F32 (bit 4), A = B = BF16 (bits 7, 10), both K-major, N>>3 at 17, M>>4 at 24
 constexpr uint32_t IDESC_BF16 = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) |
                                 ((uint32_t)(BM >> 4) << 24);
@@ -321,9 +223,9 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(tmem_slot)));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
   }
-  tc_fence_before();
+  fence_before();
   __syncthreads();
-  tc_fence_after();
+  fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
@@ -374,11 +276,11 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
         const uint32_t acc = i & 1;
         mbar_wait(bar_t_empty + 8 * acc, ((i >> 1) & 1) ^ 1);
         ++i;
-        tc_fence_after();
+        fence_after();
         const uint32_t d_tmem = tmem_base + acc * BN;
         for (int kb = 0; kb < p.KB; ++kb) {
           mbar_wait(bar_b_full + 8 * st, ph);
-          tc_fence_after();
+          fence_after();
           const uint32_t al = a_lo + ((kb * A_KB_BYTES) >> 4), bl = b_lo + ((st * B_ST_BYTES) >> 4);
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; ++k)
@@ -439,13 +341,13 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
 
       // ---- accumulator -> registers, then hand it back at once
       mbar_wait(bar_t_full + 8 * acc, t_par);
-      tc_fence_after();
+      fence_after();
       const uint32_t taddr = tmem_base + acc * BN + group * GW + ((uint32_t)(quarter * 32) << 16);
       uint32_t raw[8][GW];
 #pragma unroll
       for (int r = 0; r < 8; ++r) tmem_ld16(taddr + r * TB_W, raw[r]);
       tmem_ld_wait();
-      tc_fence_before();
+      fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_t_empty + 8 * acc);
 
@@ -573,9 +475,9 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
     }
   }
 
-  tc_fence_before();
+  fence_before();
   __syncthreads();
-  tc_fence_after();
+  fence_after();
   if (warp == 1) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base));
   }

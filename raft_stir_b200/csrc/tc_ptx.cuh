@@ -1,5 +1,5 @@
 // Inline-PTX wrappers for the tcgen05 / TMEM / TMA / mbarrier programming model (sm_100a), shared by the
-// tensor-core on-the-fly kernel (alt_tc.cu).  build_tc.cu carries its own, older copy of the same wrappers.
+// tensor-core volume build (build_tc.cu) and the tensor-core on-the-fly kernel (alt_tc.cu).
 #pragma once
 
 #include <cuda.h>
@@ -30,7 +30,7 @@ __device__ __forceinline__ bool mbar_try(uint32_t bar, uint32_t parity) {
   return ok != 0;
 }
 // Slow path of a wait, bounded: a protocol bug must surface as a launch error, never as a hung GPU.
-__device__ __noinline__ void mbar_wait_slow(uint32_t bar, uint32_t parity) {
+static __device__ __noinline__ void mbar_wait_slow(uint32_t bar, uint32_t parity) {
   unsigned long long t0 = 0;
   for (uint32_t spin = 1;; ++spin) {
     if (mbar_try(bar, parity)) return;
@@ -53,6 +53,37 @@ __device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap *map
       " [%0], [%1, {%3, %4, %5, %6}], [%2];"
       ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
       : "memory");
+}
+// L2 eviction policies: operands every CTA re-reads (keep them) / a stream written once and not read back by
+// the same kernel (let it go first).
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0,
+                                            int c1, int c2, uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
+      " [%0], [%1, {%3, %4, %5}], [%2], %6;"
+      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "l"(policy)
+      : "memory");
+}
+__device__ __forceinline__ void stg16_hint(void *dst, const uint4 &v, uint64_t policy) {
+  asm volatile("st.global.L2::cache_hint.v4.b32 [%0], {%1, %2, %3, %4}, %5;" ::"l"(dst), "r"(v.x), "r"(v.y), "r"(v.z),
+               "r"(v.w), "l"(policy)
+               : "memory");
+}
+__device__ __forceinline__ void stg8_hint(void *dst, uint32_t a, uint32_t b, uint64_t policy) {
+  asm volatile("st.global.L2::cache_hint.v2.b32 [%0], {%1, %2}, %3;" ::"l"(dst), "r"(a), "r"(b), "l"(policy) : "memory");
+}
+__device__ __forceinline__ void stg4_hint(void *dst, uint32_t a, uint64_t policy) {
+  asm volatile("st.global.L2::cache_hint.b32 [%0], %1, %2;" ::"l"(dst), "r"(a), "l"(policy) : "memory");
 }
 __device__ __forceinline__ void fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
