@@ -120,3 +120,31 @@ def test_install_into_rebinds_the_reference_names():
     assert mod.upflow8 is R.upflow8
     with __import__("pytest").raises(RuntimeError):          # now routed to the library, which rejects CPU tensors
         FakeRAFT().upsample_flow(__import__("torch").zeros(1, 2, 4, 4), __import__("torch").zeros(1, 576, 4, 4))
+
+
+def test_header_is_plain_c_and_links(tmp_path):
+    """include/raft_corr.h compiles as C (no C++, no torch, no CUDA headers needed by a caller) and a C program linked
+    against libraftcorr.so can call the host-only entry points."""
+    import shutil
+    import subprocess
+
+    from raft_stir_b200 import _lib
+    gcc = shutil.which("gcc")
+    if gcc is None:
+        pytest.skip("gcc not available")
+    src = tmp_path / "abi.c"
+    src.write_text(
+        '#include <stdio.h>\n#include "raft_corr.h"\n'
+        "int main(void) {\n"
+        "  rc_layout lay;\n"
+        "  int r = rc_pyramid_layout(2, 55, 128, 4, RC_VOL_BF16, &lay);\n"
+        '  printf("%d %d %d %lld %d\\n", rc_abi_version(), r, lay.num_levels, (long long)lay.total_elems, lay.elem_bytes);\n'
+        "  return r;\n}\n")
+    exe = tmp_path / "abi"
+    libdir = os.path.dirname(_lib.LIB_PATH)
+    subprocess.run([gcc, "-std=c99", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe),
+                    "-L", libdir, "-l:libraftcorr.so", f"-Wl,-rpath,{libdir}"], check=True, capture_output=True)
+    out = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()
+    lay = _lib.pyramid_layout(2, 55, 128, 4, _lib.RC_VOL_BF16)
+    assert int(out[0]) == _lib.lib().rc_abi_version() and int(out[1]) == 0
+    assert int(out[2]) == 4 and int(out[3]) == int(lay.total_elems) and int(out[4]) == 2
