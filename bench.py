@@ -403,6 +403,8 @@ def run_extras(R, device, args, pk):
             blk = R.CorrBlock(f1, f2, LEVELS, RADIUS, storage=args.storage)
             out["b1_lookup_ms"] = timeit(lambda: blk(coords[0]), 50)
             out["b1_build_fp32_simt_ms"] = timeit(lambda: R.CorrBlock(f1, f2, LEVELS, RADIUS, storage="fp32", math="fp32"), 3)
+            out["b1_build_tf32_fp32_storage_ms"] = timeit(lambda: R.CorrBlock(f1, f2, LEVELS, RADIUS, storage="fp32", math="tf32"), 10)
+            out["b1_build_bf16_fp32_storage_ms"] = timeit(lambda: R.CorrBlock(f1, f2, LEVELS, RADIUS, storage="fp32", math="bf16"), 10)
             alt = R.AlternateCorrBlock(f1, f2, LEVELS, RADIUS)
             out["b1_alt_lookup_ms"] = timeit(lambda: alt(coords[0]), 10)
             alt_tc = R.AlternateCorrBlock(f1, f2, LEVELS, RADIUS, math="bf16")

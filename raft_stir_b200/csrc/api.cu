@@ -136,7 +136,6 @@ int rc_build_pyramid(const float *fmap1, const float *fmap2, int B, int D, int H
   if (r) return r;
   cudaStream_t s = (cudaStream_t)stream;
   if (math == RC_MATH_F32) return launch_build_simt(fmap1, fmap2, B, D, H, W, lay, vol_dtype, pyramid, s);
-  RC_REQUIRE(math == RC_MATH_BF16, "RC_MATH_TF32 is declared but not built in this version");
   const int64_t need = rc_build_workspace_bytes(B, D, H, W, math);
   if (workspace == nullptr || (int64_t)workspace_bytes < need) {
     set_error("rc_build_pyramid: workspace of %zu bytes, need %lld", workspace_bytes, (long long)need);
@@ -144,7 +143,7 @@ int rc_build_pyramid(const float *fmap1, const float *fmap2, int B, int D, int H
   }
   RC_REQUIRE(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
   RC_REQUIRE(((uintptr_t)pyramid & 255) == 0, "pyramid must be 256-byte aligned");
-  const int64_t es = 2;
+  const int64_t es = math == RC_MATH_BF16 ? 2 : 4;
   void *f1p = workspace;
   void *f2p = (char *)workspace + round_up64((int64_t)B * H * W * D * es, 1024);
   r = launch_pack(fmap1, fmap2, B, D, H, W, math, f1p, f2p, s);

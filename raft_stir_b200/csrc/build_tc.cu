@@ -36,8 +36,8 @@ namespace {
 
 constexpr int BM = 128;          // queries per tile (UMMA M)
 constexpr int BN = TB_N;         // 256 targets per tile (UMMA N)
-constexpr int BK = 64;           // bf16 elements per k-block (128 bytes = swizzle span)
-constexpr int UMMA_K = 16;
+constexpr int BK = 64;           // bf16 elements per k-block (128 bytes = swizzle span); kind::tf32: 32 fp32
+constexpr int UMMA_K = 16;       // bf16 elements per MMA (32 bytes); kind::tf32: 8 fp32, the same 32 bytes
 constexpr int A_KB_BYTES = BM * 128;   // 16 KB
 constexpr int B_ST_BYTES = BN * 128;   // 32 KB
 constexpr int MAX_STAGES = 4;
@@ -102,6 +102,9 @@ using namespace tc;
 
 // kind::f16: D = F32 (bit 4), A = B = BF16 (bits 7, 10), both K-major, N>>3 at 17, M>>4 at 24
 constexpr uint32_t IDESC_BF16 = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) |
+                                ((uint32_t)(BM >> 4) << 24);
+// kind::tf32: the same with A = B = TF32 (format code 2)
+constexpr uint32_t IDESC_TF32 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) |
                                 ((uint32_t)(BM >> 4) << 24);
 
 // ---------------------------------------------------------------- epilogue staging
@@ -183,18 +186,24 @@ __device__ __forceinline__ void flush64(uint32_t ld_base, char *g, long long str
 }
 
 // ---------------------------------------------------------------- the kernel
-template <typename VolT, bool SCALE>
+// TF32 = false: bf16 operands (kind::f16), the query operand stationary in shared memory.
+// TF32 = true:  fp32 operands read as tf32 (kind::tf32, 32 channels per 128-byte k-block).  Twice the operand bytes
+//               do not fit next to the epilogue staging as a stationary operand, so the 16 KB query k-block rides
+//               in the ring slot with its 32 KB target k-block (one expect_tx, two TMA loads per slot).
+template <typename VolT, bool SCALE, bool TF32>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                         const TcParams p) {
   using S = Stg<VolT>;
   constexpr int ES = (int)sizeof(VolT);
+  constexpr int BKE = TF32 ? BK / 2 : BK;                                   // operand elements per k-block
+  constexpr uint32_t SLOT = TF32 ? A_KB_BYTES + B_ST_BYTES : B_ST_BYTES;    // bytes per ring slot
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // carve (operand offsets are multiples of 1024)
   uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const uint32_t sA = smem_u32(smem);
-  const uint32_t sB = sA + p.KB * A_KB_BYTES;
-  const uint32_t sStage = sB + p.stages * B_ST_BYTES;
+  const uint32_t sB = TF32 ? sA : sA + p.KB * A_KB_BYTES;
+  const uint32_t sStage = sB + p.stages * SLOT;
   const uint32_t sBar = sStage + EPI_WARPS * STAGE_BYTES_PER_WARP;
   uint32_t *tmem_slot = (uint32_t *)(smem + (sBar - sA) + 128);
   // barrier table (8 bytes each)
@@ -240,18 +249,19 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
       uint32_t st = 0, ph = 0;               // B ring: stage, parity of its current round
       while (walk.next(p, b, m, n, by, bx)) {
         const int key = b * p.MT + m;
-        if (key != cur_key) {
+        if (!TF32 && key != cur_key) {
           if (a_loaded) { mbar_wait(bar_a_empty, a_par); a_par ^= 1; }
           mbar_expect_tx(bar_a_full, p.KB * A_KB_BYTES);
           for (int kb = 0; kb < p.KB; ++kb)
-            tma_load_3d(sA + kb * A_KB_BYTES, &map_a, bar_a_full, kb * BK, m * BM, b, pol_in);
+            tma_load_3d(sA + kb * A_KB_BYTES, &map_a, bar_a_full, kb * BKE, m * BM, b, pol_in);
           a_loaded = true;
           cur_key = key;
         }
         for (int kb = 0; kb < p.KB; ++kb) {
           mbar_wait(bar_b_empty + 8 * st, ph ^ 1);
-          mbar_expect_tx(bar_b_full + 8 * st, B_ST_BYTES);
-          tma_load_3d(sB + st * B_ST_BYTES, &map_b, bar_b_full + 8 * st, kb * BK, n * BN, b, pol_in);
+          mbar_expect_tx(bar_b_full + 8 * st, SLOT);
+          if (TF32) tma_load_3d(sB + st * SLOT, &map_a, bar_b_full + 8 * st, kb * BKE, m * BM, b, pol_in);
+          tma_load_3d(sB + st * SLOT + (TF32 ? A_KB_BYTES : 0), &map_b, bar_b_full + 8 * st, kb * BKE, n * BN, b, pol_in);
           if (++st == (uint32_t)p.stages) { st = 0; ph ^= 1; }
         }
       }
@@ -268,7 +278,7 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
       const uint32_t a_lo = desc_lo(sA), b_lo = desc_lo(sB);
       while (walk.next(p, b, m, n, by, bx)) {
         const int key = b * p.MT + m;
-        if (key != cur_key) {
+        if (!TF32 && key != cur_key) {
           mbar_wait(bar_a_full, a_par);
           a_par ^= 1;
           cur_key = key;
@@ -281,16 +291,22 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
         for (int kb = 0; kb < p.KB; ++kb) {
           mbar_wait(bar_b_full + 8 * st, ph);
           fence_after();
-          const uint32_t al = a_lo + ((kb * A_KB_BYTES) >> 4), bl = b_lo + ((st * B_ST_BYTES) >> 4);
+          const uint32_t al = TF32 ? b_lo + ((st * SLOT) >> 4) : a_lo + ((kb * A_KB_BYTES) >> 4);
+          const uint32_t bl = b_lo + ((st * SLOT + (TF32 ? A_KB_BYTES : 0)) >> 4);
 #pragma unroll
-          for (int k = 0; k < BK / UMMA_K; ++k)
-            umma_bf16(d_tmem, desc_make(al + k * ((UMMA_K * 2) >> 4)), desc_make(bl + k * ((UMMA_K * 2) >> 4)),
-                      IDESC_BF16, (kb | k) != 0);
+          for (int k = 0; k < BK / UMMA_K; ++k) {      // four MMAs of 32 operand bytes per k-block, either kind
+            if (TF32)
+              umma_tf32(d_tmem, desc_make(al + k * ((UMMA_K * 2) >> 4)), desc_make(bl + k * ((UMMA_K * 2) >> 4)),
+                        IDESC_TF32, (kb | k) != 0);
+            else
+              umma_bf16(d_tmem, desc_make(al + k * ((UMMA_K * 2) >> 4)), desc_make(bl + k * ((UMMA_K * 2) >> 4)),
+                        IDESC_BF16, (kb | k) != 0);
+          }
           umma_commit(bar_b_empty + 8 * st);   // frees the B stage when these MMAs retire
           if (++st == (uint32_t)p.stages) { st = 0; ph ^= 1; }
         }
         umma_commit(bar_t_full + 8 * acc);     // accumulator ready
-        if (walk.a_changes(b, m)) umma_commit(bar_a_empty);   // last use of this A operand
+        if (!TF32 && walk.a_changes(b, m)) umma_commit(bar_a_empty);   // last use of this A operand
       }
     }
   } else {
@@ -519,9 +535,12 @@ int encode(CUtensorMap *map, CUtensorMapDataType dt, int rank, const void *base,
   return RC_OK;
 }
 
-template <typename VolT>
+template <typename VolT, bool TF32>
 int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, const rc_layout &lay,
                VolT *pyr, cudaStream_t s) {
+  constexpr int BKE = TF32 ? BK / 2 : BK;
+  constexpr int OPB = TF32 ? 4 : 2;                 // operand bytes per element
+  constexpr size_t SLOT = TF32 ? A_KB_BYTES + B_ST_BYTES : B_ST_BYTES;
   const int N = H * W;
   const int L = lay.num_levels;
   if (L > 4) {
@@ -538,7 +557,7 @@ int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, con
   p.MT = ceil_div(N, BM);
   p.nbx = ceil_div(W, TB_W);
   p.NT = p.nbx * ceil_div(H, TB_H);
-  p.KB = ceil_div(D, BK);
+  p.KB = ceil_div(D, BKE);
   p.num_levels = L;
   float pre_scale = 1.f;
   split_scale(D, &pre_scale, &p.scale);      // pre_scale was applied to fmap1 by the pack
@@ -557,10 +576,10 @@ int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, con
   RC_CUDA(cudaGetDevice(&dev));
   RC_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   RC_CUDA(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
-  const size_t fixed = (size_t)p.KB * A_KB_BYTES + (size_t)EPI_WARPS * STAGE_BYTES_PER_WARP + 256 + 1024;
+  const size_t fixed = (TF32 ? 0 : (size_t)p.KB * A_KB_BYTES) + (size_t)EPI_WARPS * STAGE_BYTES_PER_WARP + 256 + 1024;
   p.stages = 0;
   for (int st = MAX_STAGES; st >= 2; --st)
-    if (fixed + (size_t)st * B_ST_BYTES <= (size_t)max_smem) {
+    if (fixed + (size_t)st * SLOT <= (size_t)max_smem) {
       p.stages = st;
       break;
     }
@@ -568,7 +587,7 @@ int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, con
     set_error("D = %d does not fit the tensor-core build's shared memory budget", D);
     return RC_EINVAL;
   }
-  const size_t smem = fixed + (size_t)p.stages * B_ST_BYTES;
+  const size_t smem = fixed + (size_t)p.stages * SLOT;
 
   // pairs per group: about one query block's worth of tiles per CTA and group
   const long long tpp = (long long)p.MT * p.NT;
@@ -581,20 +600,22 @@ int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, con
   CUtensorMap ma, mb;
   {
     cuuint64_t dims[3] = {(cuuint64_t)D, (cuuint64_t)N, (cuuint64_t)B};
-    cuuint64_t str[2] = {(cuuint64_t)D * 2, (cuuint64_t)N * D * 2};
-    cuuint32_t box[3] = {BK, BM, 1};
-    int r = encode(&ma, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, f1p, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B, "fmap1");
+    cuuint64_t str[2] = {(cuuint64_t)D * OPB, (cuuint64_t)N * D * OPB};
+    cuuint32_t box[3] = {BKE, BM, 1};
+    int r = encode(&ma, TF32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, f1p, dims, str, box,
+                   CU_TENSOR_MAP_SWIZZLE_128B, "fmap1");
     if (r) return r;
   }
   {
     cuuint64_t dims[3] = {(cuuint64_t)D, (cuuint64_t)rows2, (cuuint64_t)B};
-    cuuint64_t str[2] = {(cuuint64_t)D * 2, (cuuint64_t)rows2 * D * 2};
-    cuuint32_t box[3] = {BK, BN, 1};
-    int r = encode(&mb, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, f2p, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B, "fmap2");
+    cuuint64_t str[2] = {(cuuint64_t)D * OPB, (cuuint64_t)rows2 * D * OPB};
+    cuuint32_t box[3] = {BKE, BN, 1};
+    int r = encode(&mb, TF32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, f2p, dims, str, box,
+                   CU_TENSOR_MAP_SWIZZLE_128B, "fmap2");
     if (r) return r;
   }
 
-  auto kern = p.scale == 1.f ? build_pyramid_tc_kernel<VolT, false> : build_pyramid_tc_kernel<VolT, true>;
+  auto kern = p.scale == 1.f ? build_pyramid_tc_kernel<VolT, false, TF32> : build_pyramid_tc_kernel<VolT, true, TF32>;
   RC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const long long group_tiles = (long long)p.group_pairs * tpp;
   const int grid = group_tiles < sms ? (int)group_tiles : sms;
@@ -607,13 +628,17 @@ int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, con
 
 int launch_build_tc(const void *f1p, const void *f2p, int B, int D, int H, int W, const rc_layout &lay,
                     int vol_dtype, int math, void *pyramid, cudaStream_t s) {
+  if (math == RC_MATH_TF32)
+    return vol_dtype == RC_VOL_BF16
+               ? build_tc_t<__nv_bfloat16, true>(f1p, f2p, B, D, H, W, lay, (__nv_bfloat16 *)pyramid, s)
+               : build_tc_t<float, true>(f1p, f2p, B, D, H, W, lay, (float *)pyramid, s);
   if (math != RC_MATH_BF16) {
-    set_error("tensor-core build: only RC_MATH_BF16 is implemented (math=%d)", math);
+    set_error("tensor-core build: math=%d is not a tensor-core mode", math);
     return RC_EINVAL;
   }
   return vol_dtype == RC_VOL_BF16
-             ? build_tc_t<__nv_bfloat16>(f1p, f2p, B, D, H, W, lay, (__nv_bfloat16 *)pyramid, s)
-             : build_tc_t<float>(f1p, f2p, B, D, H, W, lay, (float *)pyramid, s);
+             ? build_tc_t<__nv_bfloat16, false>(f1p, f2p, B, D, H, W, lay, (__nv_bfloat16 *)pyramid, s)
+             : build_tc_t<float, false>(f1p, f2p, B, D, H, W, lay, (float *)pyramid, s);
 }
 
 }  // namespace rc

@@ -27,9 +27,15 @@ template <>
 __device__ __forceinline__ void store_pair<__nv_bfloat16>(__nv_bfloat16 *p, float a, float b) {
   *reinterpret_cast<__nv_bfloat162 *>(p) = __floats2bfloat162_rn(a, b);
 }
+// fp32 operands feed kind::tf32, which reads the top 19 bits and ignores the rest (truncation): round to nearest here
+__device__ __forceinline__ float round_tf32(float v) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
+  return __uint_as_float(r);
+}
 template <>
 __device__ __forceinline__ void store_pair<float>(float *p, float a, float b) {
-  *reinterpret_cast<float2 *>(p) = make_float2(a, b);
+  *reinterpret_cast<float2 *>(p) = make_float2(round_tf32(a), round_tf32(b));
 }
 
 // grid: (row_groups_f1 + row_groups_f2, D/PK_D, B); block: 256 threads

@@ -79,6 +79,37 @@ def test_build_tensor_core_matches_reference(golden, storage):
         rel_close(v[:, 0].float().cpu().numpy(), pyr[l], tol, f"bf16-exact/{storage} level {l}")
 
 
+def tf32_round(a):
+    """fp32 -> tf32 (10 mantissa bits), round to nearest with ties away from zero: what cvt.rna.tf32.f32 does."""
+    u = np.ascontiguousarray(a, np.float32).view(np.uint32).astype(np.uint64)
+    u = ((u + 0x1000) & 0xFFFFE000).astype(np.uint32)
+    return u.view(np.float32)
+
+
+@pytest.mark.parametrize("shape", [(1, 256, 55, 128), (2, 128, 46, 62), (1, 64, 17, 33), (3, 40, 8, 9), (2, 32, 24, 30)])
+def test_build_tf32_vs_oracle_shapes(shape):
+    """math="tf32" (tcgen05 kind::tf32 on the fp32 features rounded to tf32), fp32 storage: equal to the oracle fed
+    the same tf32-rounded features up to fp32 summation order, and within 1e-3 (2^-10-mantissa operands) of the
+    unrounded fp32 oracle, relative to the magnitude a dot product of that length is accurate to."""
+    B, D, H, W = shape
+    rng = np.random.default_rng(H * W + D + 1)
+    f1 = rng.standard_normal(shape).astype(np.float32)
+    f2 = rng.standard_normal(shape).astype(np.float32)
+    L = 4 if min(H, W) >= 8 else 3
+    blk = R.CorrBlock(t(f1), t(f2), L, 4, storage="fp32", math="tf32")
+    # (the pack's power-of-two pre-scale of fmap1 commutes with the rounding)
+    pyr = O.corr_pyramid(tf32_round(f1).astype(np.float64), tf32_round(f2).astype(np.float64), L)
+    for l, v in enumerate(blk.corr_pyramid):
+        rel_close(v[:, 0].float().cpu().numpy(), pyr[l], 2e-5, f"tf32-exact {shape} level {l}")
+    ref = O.corr_pyramid(f1, f2, L)
+    for l, v in enumerate(blk.corr_pyramid):
+        rel_close(v[:, 0].float().cpu().numpy(), ref[l], 1e-3, f"tf32 {shape} level {l} vs fp32", floor=bf16_floor(f1, f2))
+    # and a lookup on it agrees with the fp32 block to the same class
+    coords = t((O.coords_grid(B, H, W) + rng.normal(0, 3, (B, 2, H, W))).astype(np.float32))
+    want = R.CorrBlock(t(f1), t(f2), L, 4, storage="fp32", math="fp32")(coords)
+    rel_close(blk(coords).cpu().numpy(), want.cpu().numpy(), 1e-3, f"tf32 lookup {shape}", floor=bf16_floor(f1, f2))
+
+
 @pytest.mark.parametrize("shape", [(1, 256, 55, 128), (2, 128, 46, 62), (1, 64, 17, 33), (3, 32, 8, 9), (2, 32, 24, 30),
                                    (1, 32, 9, 240)])
 @pytest.mark.parametrize("storage", ["bf16", "fp32"])

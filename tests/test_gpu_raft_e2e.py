@@ -65,6 +65,13 @@ def test_flow_with_library_upsampling(reference_run):
     assert d <= 0.01, f"mean EPE delta {d:.5f} px > 0.01 px"
 
 
+def test_flow_with_tf32_build_fp32_volume(reference_run):
+    nets, im1, im2, low, up = reference_run
+    _, got = Hn.raft_forward(nets, im1, im2, iters=12, corr_cls=partial(R.CorrBlock, storage="fp32", math="tf32"))
+    d = _epe(got, up)
+    assert d <= 0.002, f"mean EPE delta {d:.5f} px with the tf32 build (bf16 build: ~0.0023, fp32: ~0.0003)"
+
+
 def test_flow_with_fp32_volume(reference_run):
     nets, im1, im2, low, up = reference_run
     _, got = Hn.raft_forward(nets, im1, im2, iters=12, corr_cls=partial(R.CorrBlock, storage="fp32", math="fp32"))
