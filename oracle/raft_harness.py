@@ -19,16 +19,47 @@ import torch.nn.functional as F
 HERE = os.path.dirname(os.path.abspath(__file__))
 REF_DIR = os.path.join(HERE, "_ref")
 FILES = ("raft_basic_fnet.pt", "raft_basic_cnet.pt", "raft_basic_update.pt")
+SMALL_FILES = ("raft_small_fnet.pt", "raft_small_cnet.pt", "raft_small_update.pt")
 HDIM = CDIM = 128   # core/raft.py:35-36
+SMALL_HDIM, SMALL_CDIM, SMALL_RADIUS = 96, 64, 3   # core/raft.py:29-33
 
 
-def available() -> bool:
-    return all(os.path.exists(os.path.join(REF_DIR, f)) for f in FILES)
+def available(small: bool = False) -> bool:
+    return all(os.path.exists(os.path.join(REF_DIR, f)) for f in (SMALL_FILES if small else FILES))
 
 
-def load(device):
-    """(fnet, cnet, update_block) TorchScript modules on `device`."""
-    return tuple(torch.jit.load(os.path.join(REF_DIR, f), map_location=device).eval() for f in FILES)
+def load(device, small: bool = False):
+    """(fnet, cnet, update_block) TorchScript modules on `device` (RAFT-basic, or RAFT-small)."""
+    return tuple(torch.jit.load(os.path.join(REF_DIR, f), map_location=device).eval()
+                 for f in (SMALL_FILES if small else FILES))
+
+
+def upflow8(flow):
+    """core/utils/utils.py:80-82"""
+    return 8 * F.interpolate(flow, size=(8 * flow.shape[2], 8 * flow.shape[3]), mode="bilinear", align_corners=True)
+
+
+@torch.no_grad()
+def raft_small_forward(nets, image1, image2, iters=12, corr_cls=None, upflow_fn=None):
+    """RAFT.forward(test_mode=True) of the SMALL model (core/raft.py:86-144 with args.small): D = 128 features,
+    correlation radius 3, no upsampling mask -> upflow8 (core/raft.py:131-133)."""
+    fnet, cnet, update = nets
+    corr_cls = corr_cls or TorchCorrBlock
+    image1 = (2 * (image1 / 255.0) - 1.0).contiguous()
+    image2 = (2 * (image2 / 255.0) - 1.0).contiguous()
+    B = image1.shape[0]
+    fmaps = fnet(torch.cat([image1, image2], dim=0)).float()
+    corr_fn = corr_cls(fmaps[:B], fmaps[B:], radius=SMALL_RADIUS)
+    net, inp = torch.split(cnet(image1), [SMALL_HDIM, SMALL_CDIM], dim=1)
+    net, inp = torch.tanh(net), torch.relu(inp)
+    H8, W8 = image1.shape[2] // 8, image1.shape[3] // 8
+    coords0 = coords_grid(B, H8, W8, image1.device)
+    coords1 = coords0.clone()
+    for _ in range(iters):
+        corr = corr_fn(coords1)
+        net, delta = update(net, inp, corr, coords1 - coords0)     # the traced wrapper drops the None mask
+        coords1 = coords1 + delta
+    return coords1 - coords0, (upflow_fn or upflow8)(coords1 - coords0)
 
 
 def coords_grid(batch, ht, wd, device):

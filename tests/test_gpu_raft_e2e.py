@@ -132,3 +132,24 @@ def test_training_gradients_through_the_block():
     rel = ((a - b).norm() / a.norm()).item()
     cos = torch.nn.functional.cosine_similarity(a, b, dim=0).item()
     assert cos > 0.999 and rel < 3 * floor + 2e-3, f"gradient difference {rel:.2e} (cos {cos:.5f}); 1e-7 jitter floor {floor:.2e}"
+
+
+def test_raft_small_with_library_block_and_upflow8():
+    """RAFT-small end to end (core/raft.py:29-33, :48-51): 128-channel features, radius-3 lookup, no mask so the flow
+    leaves through upflow8.  Traced small sub-networks around (a) the reference block's torch ops + F.interpolate and
+    (b) this library's CorrBlock (bf16 tensor-core build, post-scaled since 128 is not a power of 4) + rc_upflow8."""
+    if not Hn.available(small=True):
+        pytest.skip("oracle/_ref/raft_small_*.pt not built")
+    dev = torch.device("cuda:0")
+    nets = Hn.load(dev, small=True)
+    im1, im2 = _inputs(1, 440, 1024, dev)
+    _, ref = Hn.raft_small_forward(nets, im1, im2, iters=12)
+    assert torch.isfinite(ref).all()
+    _, got = Hn.raft_small_forward(nets, im1, im2, iters=12, corr_cls=R.CorrBlock, upflow_fn=R.upflow8)
+    d = _epe(got, ref)
+    assert d <= 0.01, f"RAFT-small: mean EPE delta {d:.5f} px > 0.01 px (mean |flow| {ref.norm(dim=1).mean().item():.2f} px)"
+    _, got = Hn.raft_small_forward(nets, im1, im2, iters=12, corr_cls=partial(R.CorrBlock, storage="fp32", math="tf32"),
+                                   upflow_fn=R.upflow8)
+    d32 = _epe(got, ref)
+    assert d32 <= 0.002, f"RAFT-small, tf32 build: mean EPE delta {d32:.5f} px"
+
