@@ -592,6 +592,7 @@ int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, con
   // pairs per group: about one query block's worth of tiles per CTA and group
   const long long tpp = (long long)p.MT * p.NT;
   long long gp = ((long long)p.NT * sms + tpp - 1) / tpp;
+  if (TF32) gp = (gp + 1) / 2;            // fp32 operands: twice the bytes to keep hot in L2 per pair
   if (gp < 1) gp = 1;
   if (gp > B) gp = B;
   p.group_pairs = (int)gp;
