@@ -71,7 +71,7 @@ static int make_layout(int B, int H, int W, int num_levels, int vol_dtype, rc_la
   RC_REQUIRE(B >= 1 && H >= 1 && W >= 1, "rc_pyramid_layout: bad sizes B=%d H=%d W=%d", B, H, W);
   RC_REQUIRE(num_levels >= 1 && num_levels <= RC_MAX_LEVELS, "num_levels %d outside 1..%d", num_levels,
              RC_MAX_LEVELS);
-  RC_REQUIRE(vol_dtype == RC_VOL_F32 || vol_dtype == RC_VOL_BF16, "unknown vol_dtype %d", vol_dtype);
+  RC_REQUIRE(vol_dtype == RC_VOL_F32 || vol_dtype == RC_VOL_BF16 || vol_dtype == RC_VOL_F16, "unknown vol_dtype %d", vol_dtype);
   RC_REQUIRE((H >> (num_levels - 1)) >= 1 && (W >> (num_levels - 1)) >= 1,
              "a %dx%d map has no level %d (avg_pool2d would produce an empty tensor)", H, W,
              num_levels - 1);
@@ -80,7 +80,7 @@ static int make_layout(int B, int H, int W, int num_levels, int vol_dtype, rc_la
   out->num_levels = num_levels;
   out->B = B;
   out->N = H * W;
-  out->elem_bytes = vol_dtype == RC_VOL_BF16 ? 2 : 4;
+  out->elem_bytes = vol_dtype == RC_VOL_F32 ? 4 : 2;
   // 64-byte tiles: 4 rows of 16 bytes
   out->tile_h = TILE_H;
   out->tile_w = 16 / out->elem_bytes;

@@ -22,9 +22,12 @@ template <>
 __device__ __forceinline__ float to_vol<float>(float v) { return v; }
 template <>
 __device__ __forceinline__ __nv_bfloat16 to_vol<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+template <>
+__device__ __forceinline__ __half to_vol<__half>(float v) { return __float2half_rn(clamp_half(v)); }
 
 __device__ __forceinline__ float from_vol(float v) { return v; }
 __device__ __forceinline__ float from_vol(__nv_bfloat16 v) { return __bfloat162float(v); }
+__device__ __forceinline__ float from_vol(__half v) { return __half2float(v); }
 
 // grid: (ceil(N/64) targets, ceil(N/64) queries, B); block 256 = 16x16, 4x4 outputs each
 template <typename VolT>
@@ -133,17 +136,18 @@ int pool_levels_t(const rc_layout &lay, VolT *pyr, int first_level, cudaStream_t
 
 int launch_build_simt(const float *fmap1, const float *fmap2, int B, int D, int H, int W,
                       const rc_layout &lay, int vol_dtype, void *pyramid, cudaStream_t s) {
-  int rcode = vol_dtype == RC_VOL_BF16
-                  ? build_simt_t<__nv_bfloat16>(fmap1, fmap2, B, D, H, W, lay, (__nv_bfloat16 *)pyramid, s)
-                  : build_simt_t<float>(fmap1, fmap2, B, D, H, W, lay, (float *)pyramid, s);
+  int rcode = vol_dtype == RC_VOL_BF16  ? build_simt_t<__nv_bfloat16>(fmap1, fmap2, B, D, H, W, lay, (__nv_bfloat16 *)pyramid, s)
+              : vol_dtype == RC_VOL_F16 ? build_simt_t<__half>(fmap1, fmap2, B, D, H, W, lay, (__half *)pyramid, s)
+                                        : build_simt_t<float>(fmap1, fmap2, B, D, H, W, lay, (float *)pyramid, s);
   if (rcode != RC_OK) return rcode;
   return launch_pool_levels(lay, vol_dtype, pyramid, 1, s);
 }
 
 int launch_pool_levels(const rc_layout &lay, int vol_dtype, void *pyramid, int first_level,
                        cudaStream_t s) {
-  return vol_dtype == RC_VOL_BF16 ? pool_levels_t<__nv_bfloat16>(lay, (__nv_bfloat16 *)pyramid, first_level, s)
-                                  : pool_levels_t<float>(lay, (float *)pyramid, first_level, s);
+  return vol_dtype == RC_VOL_BF16  ? pool_levels_t<__nv_bfloat16>(lay, (__nv_bfloat16 *)pyramid, first_level, s)
+         : vol_dtype == RC_VOL_F16 ? pool_levels_t<__half>(lay, (__half *)pyramid, first_level, s)
+                                   : pool_levels_t<float>(lay, (float *)pyramid, first_level, s);
 }
 
 }  // namespace rc

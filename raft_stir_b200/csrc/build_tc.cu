@@ -118,13 +118,16 @@ constexpr uint32_t IDESC_TF32 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)
 // (20 / 40 bytes per query and tile) are stored by the owning thread directly.
 template <typename VolT>
 struct Stg;
-template <>
-struct Stg<__nv_bfloat16> {
+struct Stg16 {                            // 2-byte elements (bf16, fp16)
   static constexpr int TW = 8;            // tile width, elements
   static constexpr int L0_GT = 2;         // level-0 tiles per group and row of tiles
   static constexpr int L1_GT = 1;         // level-1 tiles per group
   static constexpr int STEPS = 2;         // level-0 steps per tile
 };
+template <>
+struct Stg<__nv_bfloat16> : Stg16 {};
+template <>
+struct Stg<__half> : Stg16 {};
 template <>
 struct Stg<float> {
   static constexpr int TW = 4;
@@ -144,15 +147,11 @@ __device__ __forceinline__ uint4 lds16(uint32_t addr) {
   asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
   return v;
 }
-__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
-  __nv_bfloat162 p = __floats2bfloat162_rn(a, b);
-  return *reinterpret_cast<uint32_t *>(&p);
-}
 // one 16-byte unit (8 bf16 or 4 fp32 values) -> shared memory
 template <typename VolT>
 __device__ __forceinline__ void put_unit(uint32_t addr, const float *v) {
   if (sizeof(VolT) == 2)
-    sts16(addr, pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+    sts16(addr, pack2<VolT>(v[0], v[1]), pack2<VolT>(v[2], v[3]), pack2<VolT>(v[4], v[5]), pack2<VolT>(v[6], v[7]));
   else
     sts16(addr, __float_as_uint(v[0]), __float_as_uint(v[1]), __float_as_uint(v[2]), __float_as_uint(v[3]));
 }
@@ -422,7 +421,7 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
           if (L > 2 && lane < nq && (y0 >> 4) < p.tiles_y[2] && x2 / S::TW < p.tiles_x[2]) {
             char *g2 = (char *)p.lvl[2] + ((long long)(y0 >> 4) * p.tiles_x[2] + x2 / S::TW) * 64 +
                        (slab_q0 + lane) * p.slab[2] * ES + (((y0 >> 2) & 3) + (rp >> 1)) * 16 + (x2 % S::TW) * ES;
-            if (ES == 2) stg8_hint(g2, pack_bf16(p2[0], p2[1]), pack_bf16(p2[2], p2[3]), pol_out);
+            if (ES == 2) stg8_hint(g2, pack2<VolT>(p2[0], p2[1]), pack2<VolT>(p2[2], p2[3]), pol_out);
             else stg16_hint(g2, make_uint4(__float_as_uint(p2[0]), __float_as_uint(p2[1]), __float_as_uint(p2[2]),
                                            __float_as_uint(p2[3])), pol_out);
           }
@@ -439,7 +438,7 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
               char *g3 = (char *)p.lvl[3] + ((long long)(y0 >> 5) * p.tiles_x[3] + x3 / S::TW) * 64 +
                          (slab_q0 + lane) * p.slab[3] * ES + ((y0 >> 3) & 3) * 16 + (x3 % S::TW) * ES;
               if (ES == 2) {
-                stg4_hint(g3, pack_bf16(p3[0], p3[1]), pol_out);
+                stg4_hint(g3, pack2<VolT>(p3[0], p3[1]), pol_out);
                 // a bf16 tile row holds the cells of two blocks; with no block to the right, its
                 // cells 4..7 are padding columns and must read as zero
                 if (group == 1 && !(bx & 1) && bx + 1 >= p.nbx) stg8_hint(g3 + 4, 0u, 0u, pol_out);
@@ -630,16 +629,16 @@ int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, con
 int launch_build_tc(const void *f1p, const void *f2p, int B, int D, int H, int W, const rc_layout &lay,
                     int vol_dtype, int math, void *pyramid, cudaStream_t s) {
   if (math == RC_MATH_TF32)
-    return vol_dtype == RC_VOL_BF16
-               ? build_tc_t<__nv_bfloat16, true>(f1p, f2p, B, D, H, W, lay, (__nv_bfloat16 *)pyramid, s)
-               : build_tc_t<float, true>(f1p, f2p, B, D, H, W, lay, (float *)pyramid, s);
+    return vol_dtype == RC_VOL_BF16  ? build_tc_t<__nv_bfloat16, true>(f1p, f2p, B, D, H, W, lay, (__nv_bfloat16 *)pyramid, s)
+           : vol_dtype == RC_VOL_F16 ? build_tc_t<__half, true>(f1p, f2p, B, D, H, W, lay, (__half *)pyramid, s)
+                                     : build_tc_t<float, true>(f1p, f2p, B, D, H, W, lay, (float *)pyramid, s);
   if (math != RC_MATH_BF16) {
     set_error("tensor-core build: math=%d is not a tensor-core mode", math);
     return RC_EINVAL;
   }
-  return vol_dtype == RC_VOL_BF16
-             ? build_tc_t<__nv_bfloat16, false>(f1p, f2p, B, D, H, W, lay, (__nv_bfloat16 *)pyramid, s)
-             : build_tc_t<float, false>(f1p, f2p, B, D, H, W, lay, (float *)pyramid, s);
+  return vol_dtype == RC_VOL_BF16  ? build_tc_t<__nv_bfloat16, false>(f1p, f2p, B, D, H, W, lay, (__nv_bfloat16 *)pyramid, s)
+         : vol_dtype == RC_VOL_F16 ? build_tc_t<__half, false>(f1p, f2p, B, D, H, W, lay, (__half *)pyramid, s)
+                                   : build_tc_t<float, false>(f1p, f2p, B, D, H, W, lay, (float *)pyramid, s);
 }
 
 }  // namespace rc

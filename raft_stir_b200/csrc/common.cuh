@@ -2,6 +2,7 @@
 #pragma once
 
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <math.h>
@@ -80,6 +81,34 @@ struct Tile {
   static constexpr int LOG_W = sizeof(VolT) == 2 ? 3 : 2;
   static constexpr int ELEMS = TILE_H * W;             // elements per tile
 };
+// Conversions between fp32 and the stored element type: two 16-bit elements per 32-bit word (first element low).
+template <typename VolT>
+__device__ __forceinline__ uint32_t pack2(float a, float b);
+template <>
+__device__ __forceinline__ uint32_t pack2<__nv_bfloat16>(float a, float b) {
+  __nv_bfloat162 p = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t *>(&p);
+}
+// fp16 storage saturates at the largest finite half instead of overflowing to infinity
+__device__ __forceinline__ float clamp_half(float v) { return fminf(fmaxf(v, -65504.f), 65504.f); }
+template <>
+__device__ __forceinline__ uint32_t pack2<__half>(float a, float b) {
+  __half2 p = __floats2half2_rn(clamp_half(a), clamp_half(b));
+  return *reinterpret_cast<uint32_t *>(&p);
+}
+template <>
+__device__ __forceinline__ uint32_t pack2<float>(float a, float) { return __float_as_uint(a); }   // unused for 4-byte storage
+template <typename VolT>
+__device__ __forceinline__ float2 unpack2(uint32_t w);
+template <>
+__device__ __forceinline__ float2 unpack2<__nv_bfloat16>(uint32_t w) {
+  return make_float2(__uint_as_float(w << 16), __uint_as_float(w & 0xffff0000u));
+}
+template <>
+__device__ __forceinline__ float2 unpack2<__half>(uint32_t w) { return __half22float2(*reinterpret_cast<__half2 *>(&w)); }
+template <>
+__device__ __forceinline__ float2 unpack2<float>(uint32_t w) { return make_float2(__uint_as_float(w), 0.f); }   // unused
+
 // element offset of (y, x) inside one query's slab
 template <typename VolT>
 __host__ __device__ inline long long tile_offset(int y, int x, int tiles_x) {

@@ -212,9 +212,9 @@ __device__ __forceinline__ void read_row(uint32_t win, int lane, int j, int o, u
     const int sh = (o & 1) * 16;
 #pragma unroll
     for (int k = 0; k < T / 2; ++k) {
-      const uint32_t pr = __funnelshift_r(ys[k], ys[k + 1], sh);
-      v[2 * k] = __uint_as_float(pr << 16);
-      v[2 * k + 1] = __uint_as_float(pr & 0xffff0000u);
+      const float2 f = unpack2<VolT>(__funnelshift_r(ys[k], ys[k + 1], sh));
+      v[2 * k] = f.x;
+      v[2 * k + 1] = f.y;
     }
   } else {
 #pragma unroll
@@ -521,6 +521,8 @@ int launch_lookup_fwd(const void *pyramid, int vol_dtype, const float *coords, c
   (void)H; (void)W;
   if (vol_dtype == RC_VOL_BF16) {
     RC_DISPATCH_R2(lookup_fwd_t, __nv_bfloat16, float, (const __nv_bfloat16 *)pyramid, coords, lay, out, s)
+  } else if (vol_dtype == RC_VOL_F16) {
+    RC_DISPATCH_R2(lookup_fwd_t, __half, float, (const __half *)pyramid, coords, lay, out, s)
   } else {
     RC_DISPATCH_R2(lookup_fwd_t, float, float, (const float *)pyramid, coords, lay, out, s)
   }
@@ -531,6 +533,8 @@ int launch_lookup_fwd_f16(const void *pyramid, int vol_dtype, const float *coord
   __half *out = (__half *)out_f16;
   if (vol_dtype == RC_VOL_BF16) {
     RC_DISPATCH_R2(lookup_fwd_t, __nv_bfloat16, __half, (const __nv_bfloat16 *)pyramid, coords, lay, out, s)
+  } else if (vol_dtype == RC_VOL_F16) {
+    RC_DISPATCH_R2(lookup_fwd_t, __half, __half, (const __half *)pyramid, coords, lay, out, s)
   } else {
     RC_DISPATCH_R2(lookup_fwd_t, float, __half, (const float *)pyramid, coords, lay, out, s)
   }
@@ -543,6 +547,9 @@ int launch_lookup_bwd(const void *pyramid, int vol_dtype, const float *coords, c
   if (vol_dtype == RC_VOL_BF16) {
     RC_DISPATCH_R(lookup_bwd_t, __nv_bfloat16, (const __nv_bfloat16 *)pyramid, coords, grad_out, lay,
                   glay, grad_pyramid, grad_coords, s)
+  } else if (vol_dtype == RC_VOL_F16) {
+    RC_DISPATCH_R(lookup_bwd_t, __half, (const __half *)pyramid, coords, grad_out, lay, glay, grad_pyramid,
+                  grad_coords, s)
   } else {
     RC_DISPATCH_R(lookup_bwd_t, float, (const float *)pyramid, coords, grad_out, lay, glay,
                   grad_pyramid, grad_coords, s)

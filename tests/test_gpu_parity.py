@@ -110,6 +110,44 @@ def test_build_tf32_vs_oracle_shapes(shape):
     rel_close(blk(coords).cpu().numpy(), want.cpu().numpy(), 1e-3, f"tf32 lookup {shape}", floor=bf16_floor(f1, f2))
 
 
+def fp16_round(a):
+    return np.asarray(a, np.float32).astype(np.float16).astype(np.float32)
+
+
+@pytest.mark.parametrize("math", ["bf16", "tf32", "fp32"])
+@pytest.mark.parametrize("shape", [(1, 256, 55, 128), (2, 128, 19, 45), (3, 32, 8, 9)])
+def test_fp16_storage_build_and_lookup(shape, math):
+    """storage="fp16" (RC_VOL_F16): every level equals the oracle's value (for the operands that math sees) rounded
+    once to IEEE half (2^-11 relative), the padding of edge tiles is zero, and the lookup on it matches the oracle's
+    lookup on the fp16-rounded pyramid to fp32 round-off; forward and d/dcoords."""
+    B, D, H, W = shape
+    rng = np.random.default_rng(H * W + D + len(math))
+    f1 = rng.standard_normal(shape).astype(np.float32)
+    f2 = rng.standard_normal(shape).astype(np.float32)
+    L = 4 if min(H, W) >= 8 else 3
+    blk = R.CorrBlock(t(f1), t(f2), L, 4, storage="fp16", math=math)
+    assert blk._buf.dtype == torch.float16
+    rnd = {"bf16": bf16_round, "tf32": tf32_round, "fp32": lambda a: a}[math]
+    pyr = O.corr_pyramid(rnd(f1).astype(np.float64), rnd(f2).astype(np.float64), L)
+    got = [v[:, 0].float().cpu().numpy() for v in blk.corr_pyramid]
+    for l in range(L):
+        # tensor-core builds pool the fp32 accumulators (one rounding per level); the CUDA-core build pools the
+        # STORED level below: roundings of values several times larger than their mean carry into the mean
+        tol = 2.0 ** -11 * 1.01 * (4 if math == "fp32" and l > 0 else 1)
+        rel_close(got[l], pyr[l], tol, f"fp16 storage {math} {shape} level {l}")
+    coords = (O.coords_grid(B, H, W) + rng.normal(0, 3, (B, 2, H, W))).astype(np.float32)
+    out = blk(t(coords)).cpu().numpy()
+    rel_close(out, O.window_lookup([g.astype(np.float64) for g in got], coords.astype(np.float64), 4), 2e-5,
+              f"lookup on fp16 storage {math} {shape}")
+    # d/dcoords through the fp16 volume (reads the forward taps)
+    c = t(coords).requires_grad_(True)
+    go = torch.randn(B, L * 81, H, W, device=dev(), generator=torch.Generator(device=dev()).manual_seed(1))
+    (dc,) = torch.autograd.grad(blk(c), (c,), go)
+    ref_dc = O.window_lookup_backward([g.astype(np.float64) for g in got], coords.astype(np.float64), 4,
+                                      go.cpu().numpy().astype(np.float64))[1]
+    rel_close(dc.cpu().numpy(), ref_dc, 1e-4, f"d/dcoords on fp16 storage {math} {shape}")
+
+
 @pytest.mark.parametrize("shape", [(1, 256, 55, 128), (2, 128, 46, 62), (1, 64, 17, 33), (3, 32, 8, 9), (2, 32, 24, 30),
                                    (1, 32, 9, 240)])
 @pytest.mark.parametrize("storage", ["bf16", "fp32"])
@@ -131,8 +169,8 @@ def test_build_tensor_core_vs_oracle_shapes(shape, storage):
                   floor=bf16_floor(f1, f2))
 
 
-@pytest.mark.parametrize("math", ["bf16", "fp32"])
-@pytest.mark.parametrize("storage", ["bf16", "fp32"])
+@pytest.mark.parametrize("math", ["bf16", "tf32", "fp32"])
+@pytest.mark.parametrize("storage", ["bf16", "fp16", "fp32"])
 def test_padding_columns_of_edge_tiles_are_zero(storage, math):
     """rc_layout's invariant: inside rows < H_l, tile columns >= W_l hold zeros
     (the lookup reads whole 16-byte tile rows and does not mask columns)."""

@@ -41,6 +41,8 @@ def main():
     ms_ref, up_ref = timeit(Hn.TorchCorrBlock, 5)
     res["torch_corrblock_on_gpu"] = {"ms": ms_ref, "pairs_per_s": 1e3 * B / ms_ref}
     for name, cls in (("ours_bf16_tensor_core", R.CorrBlock),
+                      ("ours_bf16_build_fp16_volume", partial(R.CorrBlock, storage="fp16", math="bf16")),
+                      ("ours_tf32_build_fp16_volume", partial(R.CorrBlock, storage="fp16", math="tf32")),
                       ("ours_tf32_build_fp32_volume", partial(R.CorrBlock, storage="fp32", math="tf32")),
                       ("ours_fp32", partial(R.CorrBlock, storage="fp32", math="fp32")),
                       ("ours_on_the_fly", R.AlternateCorrBlock),
