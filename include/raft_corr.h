@@ -40,7 +40,7 @@ extern "C" {
 /* storage type of the correlation volume / pyramid */
 #define RC_VOL_F32 0
 #define RC_VOL_BF16 1
-#define RC_VOL_F16 2     /* IEEE half: the bytes of bf16 with three more mantissa bits; values must stay below 65 504 */
+#define RC_VOL_F16 2     /* IEEE half: the bytes of bf16 with three more mantissa bits; saturates at +-65 504 */
 
 /* arithmetic used to form the feature dot products of the volume build */
 #define RC_MATH_F32 0    /* CUDA-core fp32 FMA: what the reference's SGEMM does */
