@@ -28,7 +28,7 @@ extern "C" {
 #define RC_API
 #endif
 
-#define RC_ABI_VERSION 2
+#define RC_ABI_VERSION 3
 #define RC_MAX_LEVELS 6
 
 /* error codes */
