@@ -12,7 +12,7 @@ from functools import partial
 
 import torch
 
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import raft_stir_b200 as R          # noqa: E402
 from oracle import raft_harness as Hn   # noqa: E402
 

@@ -5,8 +5,8 @@ iterations, sequence loss gamma 0.8, AdamW, clip 1.0), reference sub-networks (o
 per GPU; with WORLD_SIZE > 1 the networks are wrapped in DistributedDataParallel (NCCL all-reduce of the
 5.26 M parameter gradients).  Prints one JSON line on rank 0: ms per step (max over ranks) and pairs/s.
 
-    python tools/train_step_bench.py                       # 1 GPU
-    python -m torch.distributed.run --nproc-per-node 8 --master-addr 127.0.0.1 tools/train_step_bench.py
+    python tests/perf/train_step_bench.py                       # 1 GPU
+    python -m torch.distributed.run --nproc-per-node 8 --master-addr 127.0.0.1 tests/perf/train_step_bench.py
 """
 import json
 import os
@@ -15,7 +15,7 @@ import sys
 import torch
 import torch.nn as nn
 
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import raft_stir_b200 as R              # noqa: E402
 from oracle import raft_harness as Hn   # noqa: E402
 
