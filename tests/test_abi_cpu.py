@@ -79,6 +79,11 @@ def test_product_does_not_import_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 src = open(os.path.join(dirpath, f)).read()
                 assert "oracle" not in src, f"{f} mentions the oracle"
+    # the GPU-box scripts under tools/ do not use it either (those that do live in tests/perf/)
+    for f in os.listdir(os.path.join(ROOT, "tools")):
+        if f.endswith((".py", ".sh")):
+            src = open(os.path.join(ROOT, "tools", f)).read()
+            assert "from oracle" not in src and "import oracle" not in src, f"tools/{f} imports the oracle"
 
 
 def test_level_view_inverts_the_tile_layout():
