@@ -221,15 +221,16 @@ RC_API int rc_alt_lookup_fwd(const float *fmap1_nhwc, const float *fmap2_pyr, co
  * The same AlternateCorrBlock.__call__ (core/corr.py:74-91) on the tensor cores: per block of 8 x 16
  * queries and level, the block's local volume against the bounding box of its windows is formed with
  * tcgen05 (bf16 operands, fp32 accumulate) and the windows are read out of it.  Same output as
- * rc_alt_lookup_fwd to bf16-operand precision (1e-2 class); valid for any coordinates (a scattered
- * block only costs more chunks).  Needs D % 64 == 0.
- *   rc_alt_features_bf16 : converts what rc_alt_pool_features produced (fmap1 NHWC + fmap2 feature
- *                          pyramid, same element offsets) to bf16
+ * rc_alt_lookup_fwd to 16-bit-operand precision; valid for any coordinates (a scattered block only costs more
+ * chunks).  Needs D % 64 == 0.  operand_dtype: RC_VOL_BF16 (8-bit exponent: any feature range) or RC_VOL_F16
+ * (three more mantissa bits; features beyond +-65 504 saturate).
+ *   rc_alt_features_16 : converts what rc_alt_pool_features produced (fmap1 NHWC + fmap2 feature
+ *                        pyramid, same element offsets) to that type
  */
-RC_API int rc_alt_features_bf16(const float *fmap1_nhwc, const float *fmap2_pyr, int B, int D, int H, int W,
-                         int num_levels, void *fmap1_bf16, void *fmap2_pyr_bf16, rc_stream_t stream);
-RC_API int rc_alt_lookup_fwd_tc(const void *fmap1_bf16, const void *fmap2_pyr_bf16, const float *coords, int B,
-                         int D, int H, int W, int num_levels, int radius, float *out, rc_stream_t stream);
+RC_API int rc_alt_features_16(const float *fmap1_nhwc, const float *fmap2_pyr, int B, int D, int H, int W,
+                       int num_levels, int operand_dtype, void *fmap1_16, void *fmap2_pyr_16, rc_stream_t stream);
+RC_API int rc_alt_lookup_fwd_tc(const void *fmap1_16, const void *fmap2_pyr_16, int operand_dtype, const float *coords,
+                         int B, int D, int H, int W, int num_levels, int radius, float *out, rc_stream_t stream);
 
 /*
  * Flow upsampling to full resolution, the step after the lookup + update block in every refinement

@@ -45,8 +45,8 @@ SIGNATURES = {
     "rc_alt_feature_pyramid_elems": (_i64, [_i, _i, _i, _i, _i, C.POINTER(_i64)]),
     "rc_alt_pool_features": (_i, [_p, _p, _i, _i, _i, _i, _i, _p, _p, _p]),
     "rc_alt_lookup_fwd": (_i, [_p, _p, _p, _i, _i, _i, _i, _i, _i, _p, _p]),
-    "rc_alt_features_bf16": (_i, [_p, _p, _i, _i, _i, _i, _i, _p, _p, _p]),
-    "rc_alt_lookup_fwd_tc": (_i, [_p, _p, _p, _i, _i, _i, _i, _i, _i, _p, _p]),
+    "rc_alt_features_16": (_i, [_p, _p, _i, _i, _i, _i, _i, _i, _p, _p, _p]),
+    "rc_alt_lookup_fwd_tc": (_i, [_p, _p, _i, _p, _i, _i, _i, _i, _i, _i, _p, _p]),
     "rc_lookup_fwd_f16": (_i, [_p, _i, _p, _i, _i, _i, _i, _i, _p, _p]),
     "rc_upsample_flow": (_i, [_p, _p, _i, _i, _i, _p, _p]),
     "rc_upsample_flow_bwd": (_i, [_p, _p, _p, _i, _i, _i, _p, _p, _p]),

@@ -259,14 +259,14 @@ class AlternateCorrBlock:
     Like the reference, the output carries no autograd history."""
 
     def __init__(self, fmap1, fmap2, num_levels: int = 4, radius: int = 4, *, math: Optional[str] = None):
-        """math: "fp32" (default; CUDA-core FMA, the reference kernel's arithmetic) or "bf16" (the block's
-        local volume on the tensor cores, bf16 operands, fp32 accumulate; needs D % 64 == 0).
-        RAFT_ALT_MATH sets the default."""
+        """math: "fp32" (default; CUDA-core FMA, the reference kernel's arithmetic), "bf16" or "fp16" (the block's
+        local volume on the tensor cores, 16-bit operands, fp32 accumulate; needs D % 64 == 0; fp16 keeps three more
+        mantissa bits of the features and saturates beyond +-65 504).  RAFT_ALT_MATH sets the default."""
         self.num_levels = num_levels
         self.radius = radius
         math = math or os.environ.get("RAFT_ALT_MATH", "fp32")
-        if math not in ("fp32", "bf16"):
-            raise RaftCorrError(f"math={math!r}: expected fp32|bf16")
+        if math not in ("fp32", "bf16", "fp16"):
+            raise RaftCorrError(f"math={math!r}: expected fp32|bf16|fp16")
         self.math = math
         L = _lib.lib()
         f1 = _require_cuda_f32(fmap1.detach(), "fmap1")
@@ -286,15 +286,17 @@ class AlternateCorrBlock:
             check(L.rc_alt_pool_features(f1.data_ptr(), f2.data_ptr(), self.B, self.D, self.H, self.W,
                                          num_levels, self._f1.data_ptr(), self._f2.data_ptr(), _stream(f1)),
                   "rc_alt_pool_features")
-        if self.math == "bf16":
+        if self.math != "fp32":
             if self.D % 64:
-                raise RaftCorrError(f"math='bf16' needs D % 64 == 0 (got D={self.D})")
-            self._f1h = torch.empty(self.B, self.H, self.W, self.D, dtype=torch.bfloat16, device=self.device)
-            self._f2h = torch.empty(total, dtype=torch.bfloat16, device=self.device)
+                raise RaftCorrError(f"math={self.math!r} needs D % 64 == 0 (got D={self.D})")
+            dt = torch.bfloat16 if self.math == "bf16" else torch.float16
+            self._op_dtype = _lib.RC_VOL_BF16 if self.math == "bf16" else _lib.RC_VOL_F16
+            self._f1h = torch.empty(self.B, self.H, self.W, self.D, dtype=dt, device=self.device)
+            self._f2h = torch.empty(total, dtype=dt, device=self.device)
             with _guard(self.device):
-                check(L.rc_alt_features_bf16(self._f1.data_ptr(), self._f2.data_ptr(), self.B, self.D, self.H,
-                                             self.W, num_levels, self._f1h.data_ptr(), self._f2h.data_ptr(),
-                                             _stream(f1)), "rc_alt_features_bf16")
+                check(L.rc_alt_features_16(self._f1.data_ptr(), self._f2.data_ptr(), self.B, self.D, self.H,
+                                           self.W, num_levels, self._op_dtype, self._f1h.data_ptr(),
+                                           self._f2h.data_ptr(), _stream(f1)), "rc_alt_features_16")
         # same attribute as the reference: [(fmap1, fmap2), pooled levels ...] as NCHW views
         self.pyramid = [(fmap1, fmap2)]
         for l in range(1, num_levels):
@@ -309,10 +311,10 @@ class AlternateCorrBlock:
         n = 2 * self.radius + 1
         out = torch.empty(self.B, self.num_levels * n * n, self.H, self.W, dtype=torch.float32, device=self.device)
         with _guard(self.device):
-            if self.math == "bf16":
-                check(_lib.lib().rc_alt_lookup_fwd_tc(self._f1h.data_ptr(), self._f2h.data_ptr(), c.data_ptr(), self.B,
-                                                      self.D, self.H, self.W, self.num_levels, self.radius,
-                                                      out.data_ptr(), _stream(c)), "rc_alt_lookup_fwd_tc")
+            if self.math != "fp32":
+                check(_lib.lib().rc_alt_lookup_fwd_tc(self._f1h.data_ptr(), self._f2h.data_ptr(), self._op_dtype,
+                                                      c.data_ptr(), self.B, self.D, self.H, self.W, self.num_levels,
+                                                      self.radius, out.data_ptr(), _stream(c)), "rc_alt_lookup_fwd_tc")
             else:
                 check(_lib.lib().rc_alt_lookup_fwd(self._f1.data_ptr(), self._f2.data_ptr(), c.data_ptr(), self.B,
                                                    self.D, self.H, self.W, self.num_levels, self.radius,

@@ -44,6 +44,7 @@ constexpr int ATC_THREADS = 192;
 
 struct AtcParams {
   int B, D, H, W, num_levels, nbx, nby;
+  int half_operands;                  // 0: bf16 operands, 1: IEEE half (same kernels, other format code)
   int Hl[RC_MAX_LEVELS], Wl[RC_MAX_LEVELS];
   float out_scale;
 };
@@ -170,7 +171,7 @@ alt_tc_fwd_kernel(const __grid_constant__ AtcMaps maps, const float *__restrict_
   } else if (warp == 1) {
     // ===================================================== MMA issuer
     if (lane == 0) {
-      constexpr uint32_t IDESC = idesc_bf16(128, 256);
+      const uint32_t IDESC = p.half_operands ? idesc_f16(128, 256) : idesc_bf16(128, 256);
       uint32_t st = 0, ph = 0;
       for (int c = 0; c < nchunks; ++c) {
         const uint32_t acc = c & 1;
@@ -461,7 +462,8 @@ alt_tc_persist_kernel(const __grid_constant__ PersistMaps maps, const float *__r
           for (int c = 0, ix = 0, iy = 0; c < nchunks; ++c, ++g) {
             const uint32_t acc = g % P_NACC;
             const bool last = (l == l_end - 1) && (c == nchunks - 1);
-            const uint32_t IDESC = idesc_bf16(128, cwk.rows(iy) * cwk.cw);     // N = targets of this chunk
+            const int Nc = cwk.rows(iy) * cwk.cw;                              // N = targets of this chunk
+            const uint32_t IDESC = p.half_operands ? idesc_f16(128, Nc) : idesc_bf16(128, Nc);
             if (++ix == cwk.nx) { ix = 0; ++iy; }
             mbar_wait(t_empty + 8 * acc, ((g / P_NACC) & 1) ^ 1);
             fence_after();
@@ -634,12 +636,12 @@ alt_tc_persist_kernel(const __grid_constant__ PersistMaps maps, const float *__r
 
 namespace {
 
+template <typename OpT>
 __global__ void __launch_bounds__(256)
-f32_to_bf16_kernel(const float *__restrict__ src, __nv_bfloat16 *__restrict__ dst, long long n4) {
+f32_to_16_kernel(const float *__restrict__ src, OpT *__restrict__ dst, long long n4) {
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
     const float4 v = __ldg(reinterpret_cast<const float4 *>(src) + i);
-    __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
-    reinterpret_cast<uint2 *>(dst)[i] = make_uint2(*reinterpret_cast<uint32_t *>(&lo), *reinterpret_cast<uint32_t *>(&hi));
+    reinterpret_cast<uint2 *>(dst)[i] = make_uint2(pack2<OpT>(v.x, v.y), pack2<OpT>(v.z, v.w));
   }
 }
 
@@ -661,7 +663,7 @@ EncodeTiledFn encode_fn() {
 }
 
 // NHWC bf16 feature map as a 4-D tensor (D, W, H, B) with a (64, bw, bh, 1) box, 128-byte swizzle
-int encode_nhwc(CUtensorMap *map, const void *base, int B, int D, int H, int W, int bw, int bh) {
+int encode_nhwc(CUtensorMap *map, const void *base, int B, int D, int H, int W, int bw, int bh, int half_operands) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) {
     set_error("cuTensorMapEncodeTiled is not available from the CUDA driver");
@@ -671,7 +673,7 @@ int encode_nhwc(CUtensorMap *map, const void *base, int B, int D, int H, int W, 
   cuuint64_t str[3] = {(cuuint64_t)D * 2, (cuuint64_t)W * D * 2, (cuuint64_t)H * W * D * 2};
   cuuint32_t box[4] = {(cuuint32_t)KB, (cuuint32_t)bw, (cuuint32_t)bh, 1};
   cuuint32_t ones[4] = {1, 1, 1, 1};
-  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void *>(base), dims, str, box, ones,
+  CUresult r = fn(map, half_operands ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void *>(base), dims, str, box, ones,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
@@ -733,19 +735,22 @@ int alt_tc_launch_persistent(const PersistMaps &maps, const float *coords, float
 
 }  // namespace
 
-int launch_alt_features_bf16(const float *src, void *dst, long long elems, cudaStream_t s) {
+int launch_alt_features_16(const float *src, void *dst, long long elems, int half_operands, cudaStream_t s) {
   const long long n4 = elems / 4;
   if (n4 == 0) return RC_OK;
   const int blocks = (int)((n4 + 255) / 256 < 148LL * 8 ? (n4 + 255) / 256 : 148LL * 8);
-  f32_to_bf16_kernel<<<blocks, 256, 0, s>>>(src, (__nv_bfloat16 *)dst, n4);
-  RC_LAUNCH_CHECK("f32_to_bf16_kernel");
+  if (half_operands) f32_to_16_kernel<__half><<<blocks, 256, 0, s>>>(src, (__half *)dst, n4);
+  else f32_to_16_kernel<__nv_bfloat16><<<blocks, 256, 0, s>>>(src, (__nv_bfloat16 *)dst, n4);
+  RC_LAUNCH_CHECK("f32_to_16_kernel");
   return RC_OK;
 }
 
 int launch_alt_lookup_tc(const void *f1_bf16, const void *f2_pyr_bf16, const float *coords, int B, int D, int H,
-                         int W, int num_levels, int radius, const int64_t *off, float *out, cudaStream_t s) {
+                         int W, int num_levels, int radius, const int64_t *off, int half_operands, float *out,
+                         cudaStream_t s) {
   AtcParams p{};
   p.B = B; p.D = D; p.H = H; p.W = W; p.num_levels = num_levels;
+  p.half_operands = half_operands;
   p.nbx = ceil_div(W, QB_W); p.nby = ceil_div(H, QB_H);
   p.out_scale = 1.0f / sqrtf((float)D);
   for (int l = 0; l < RC_MAX_LEVELS; ++l) {
@@ -759,22 +764,23 @@ int launch_alt_lookup_tc(const void *f1_bf16, const void *f2_pyr_bf16, const flo
     // The nine descriptors depend only on the buffers and the shape: a block is looked up once per refinement
     // iteration with the same ones, so the last few sets are kept per host thread (descriptors are plain data
     // holding addresses: a stale entry can only be hit by a call that passes the very same buffers and shape).
-    struct Cached { const void *f1, *f2; int B, D, H, W, L; PersistMaps maps; };
+    struct Cached { const void *f1, *f2; int B, D, H, W, L, half; PersistMaps maps; };
     thread_local Cached cache[4];
     thread_local int next = 0;
     const PersistMaps *mp = nullptr;
     for (const Cached &c : cache)
-      if (c.f1 == f1_bf16 && c.f2 == f2_pyr_bf16 && c.B == B && c.D == D && c.H == H && c.W == W && c.L == num_levels)
+      if (c.f1 == f1_bf16 && c.f2 == f2_pyr_bf16 && c.B == B && c.D == D && c.H == H && c.W == W && c.L == num_levels &&
+          c.half == half_operands)
         mp = &c.maps;
     if (!mp) {
       Cached &c = cache[next];
       c.f1 = nullptr;                                     // invalid while being rewritten
-      if ((r = encode_nhwc(&c.maps.f1, f1_bf16, B, D, H, W, QB_W, QB_H))) return r;
+      if ((r = encode_nhwc(&c.maps.f1, f1_bf16, B, D, H, W, QB_W, QB_H, half_operands))) return r;
       for (int l = 0; l < RC_MAX_LEVELS; ++l) {
-        if ((r = encode_nhwc(&c.maps.f2w[l], level(l), B, D, p.Hl[l], p.Wl[l], CH_W, 2))) return r;
-        if ((r = encode_nhwc(&c.maps.f2n[l], level(l), B, D, p.Hl[l], p.Wl[l], HALF_W, 2))) return r;
+        if ((r = encode_nhwc(&c.maps.f2w[l], level(l), B, D, p.Hl[l], p.Wl[l], CH_W, 2, half_operands))) return r;
+        if ((r = encode_nhwc(&c.maps.f2n[l], level(l), B, D, p.Hl[l], p.Wl[l], HALF_W, 2, half_operands))) return r;
       }
-      c.f1 = f1_bf16; c.f2 = f2_pyr_bf16; c.B = B; c.D = D; c.H = H; c.W = W; c.L = num_levels;
+      c.f1 = f1_bf16; c.f2 = f2_pyr_bf16; c.B = B; c.D = D; c.H = H; c.W = W; c.L = num_levels; c.half = half_operands;
       next = (next + 1) % 4;
       mp = &c.maps;
     }
@@ -788,9 +794,9 @@ int launch_alt_lookup_tc(const void *f1_bf16, const void *f2_pyr_bf16, const flo
     }
   }
   AtcMaps maps;
-  if ((r = encode_nhwc(&maps.f1, f1_bf16, B, D, H, W, QB_W, QB_H))) return r;
+  if ((r = encode_nhwc(&maps.f1, f1_bf16, B, D, H, W, QB_W, QB_H, half_operands))) return r;
   for (int l = 0; l < RC_MAX_LEVELS; ++l)
-    if ((r = encode_nhwc(&maps.f2[l], level(l), B, D, p.Hl[l], p.Wl[l], CH_W, CH_H))) return r;
+    if ((r = encode_nhwc(&maps.f2[l], level(l), B, D, p.Hl[l], p.Wl[l], CH_W, CH_H, half_operands))) return r;
   switch (radius) {
     case 1: return alt_tc_launch<1>(maps, coords, out, p, s);
     case 2: return alt_tc_launch<2>(maps, coords, out, p, s);

@@ -30,9 +30,10 @@ int launch_alt_bwd(const float *fmap1, const float *fmap2, const float *coords, 
 int launch_alt_pool(const float *fmap1, const float *fmap2, int B, int D, int H, int W, int num_levels,
                     const int64_t *off, float *f1_nhwc, float *f2_pyr, cudaStream_t s);
 // alt_tc.cu
-int launch_alt_features_bf16(const float *src, void *dst, long long elems, cudaStream_t s);
+int launch_alt_features_16(const float *src, void *dst, long long elems, int half_operands, cudaStream_t s);
 int launch_alt_lookup_tc(const void *f1_bf16, const void *f2_pyr_bf16, const float *coords, int B, int D, int H,
-                         int W, int num_levels, int radius, const int64_t *off, float *out, cudaStream_t s);
+                         int W, int num_levels, int radius, const int64_t *off, int half_operands, float *out,
+                         cudaStream_t s);
 // upsample.cu
 int launch_upsample_flow(const float *flow, const float *mask, int B, int H, int W, float *out, cudaStream_t s);
 int launch_upsample_flow_bwd(const float *flow, const float *mask, const float *gout, int B, int H, int W,
@@ -289,21 +290,24 @@ int rc_alt_lookup_fwd(const float *fmap1_nhwc, const float *fmap2_pyr, const flo
                                (cudaStream_t)stream);
 }
 
-int rc_alt_features_bf16(const float *fmap1_nhwc, const float *fmap2_pyr, int B, int D, int H, int W,
-                         int num_levels, void *fmap1_bf16, void *fmap2_pyr_bf16, rc_stream_t stream) {
-  RC_REQUIRE(fmap1_nhwc && fmap2_pyr && fmap1_bf16 && fmap2_pyr_bf16, "rc_alt_features_bf16: NULL pointer");
-  RC_REQUIRE(D >= 4 && D % 4 == 0, "rc_alt_features_bf16: D=%d must be a multiple of 4", D);
+int rc_alt_features_16(const float *fmap1_nhwc, const float *fmap2_pyr, int B, int D, int H, int W,
+                       int num_levels, int operand_dtype, void *fmap1_16, void *fmap2_pyr_16, rc_stream_t stream) {
+  RC_REQUIRE(fmap1_nhwc && fmap2_pyr && fmap1_16 && fmap2_pyr_16, "rc_alt_features_16: NULL pointer");
+  RC_REQUIRE(D >= 4 && D % 4 == 0, "rc_alt_features_16: D=%d must be a multiple of 4", D);
+  RC_REQUIRE(operand_dtype == RC_VOL_BF16 || operand_dtype == RC_VOL_F16, "rc_alt_features_16: operand_dtype %d", operand_dtype);
   int64_t off[RC_MAX_LEVELS];
   const int64_t total = rc_alt_feature_pyramid_elems(B, D, H, W, num_levels, off);
-  RC_REQUIRE(total > 0, "rc_alt_features_bf16: bad sizes");
-  int r = launch_alt_features_bf16(fmap1_nhwc, fmap1_bf16, (long long)B * H * W * D, (cudaStream_t)stream);
+  RC_REQUIRE(total > 0, "rc_alt_features_16: bad sizes");
+  const int half = operand_dtype == RC_VOL_F16;
+  int r = launch_alt_features_16(fmap1_nhwc, fmap1_16, (long long)B * H * W * D, half, (cudaStream_t)stream);
   if (r) return r;
-  return launch_alt_features_bf16(fmap2_pyr, fmap2_pyr_bf16, (long long)total, (cudaStream_t)stream);
+  return launch_alt_features_16(fmap2_pyr, fmap2_pyr_16, (long long)total, half, (cudaStream_t)stream);
 }
 
-int rc_alt_lookup_fwd_tc(const void *fmap1_bf16, const void *fmap2_pyr_bf16, const float *coords, int B, int D,
-                         int H, int W, int num_levels, int radius, float *out, rc_stream_t stream) {
+int rc_alt_lookup_fwd_tc(const void *fmap1_bf16, const void *fmap2_pyr_bf16, int operand_dtype, const float *coords,
+                         int B, int D, int H, int W, int num_levels, int radius, float *out, rc_stream_t stream) {
   RC_REQUIRE(fmap1_bf16 && fmap2_pyr_bf16 && coords && out, "rc_alt_lookup_fwd_tc: NULL pointer");
+  RC_REQUIRE(operand_dtype == RC_VOL_BF16 || operand_dtype == RC_VOL_F16, "rc_alt_lookup_fwd_tc: operand_dtype %d", operand_dtype);
   RC_REQUIRE(D >= 64 && D % 64 == 0, "rc_alt_lookup_fwd_tc: D=%d must be a multiple of 64", D);
   RC_REQUIRE(radius >= 1 && radius <= 4, "radius %d unsupported (1..4)", radius);
   RC_REQUIRE(((uintptr_t)fmap1_bf16 & 127) == 0 && ((uintptr_t)fmap2_pyr_bf16 & 127) == 0,
@@ -311,8 +315,8 @@ int rc_alt_lookup_fwd_tc(const void *fmap1_bf16, const void *fmap2_pyr_bf16, con
   int64_t off[RC_MAX_LEVELS];
   RC_REQUIRE(rc_alt_feature_pyramid_elems(B, D, H, W, num_levels, off) > 0, "rc_alt_lookup_fwd_tc: bad sizes");
   RC_REQUIRE((H >> (num_levels - 1)) >= 1 && (W >> (num_levels - 1)) >= 1, "map too small for %d levels", num_levels);
-  return launch_alt_lookup_tc(fmap1_bf16, fmap2_pyr_bf16, coords, B, D, H, W, num_levels, radius, off, out,
-                              (cudaStream_t)stream);
+  return launch_alt_lookup_tc(fmap1_bf16, fmap2_pyr_bf16, coords, B, D, H, W, num_levels, radius, off,
+                              operand_dtype == RC_VOL_F16, out, (cudaStream_t)stream);
 }
 
 int rc_upsample_flow(const float *flow, const float *mask, int B, int H, int W, float *out, rc_stream_t stream) {

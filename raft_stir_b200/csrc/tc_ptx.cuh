@@ -145,6 +145,10 @@ __device__ __forceinline__ uint64_t desc_make(uint32_t lo) { return ((uint64_t)D
 constexpr uint32_t idesc_bf16(int M, int N) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
+// the same with A = B = F16 (IEEE half, format code 0)
+constexpr uint32_t idesc_f16(int M, int N) {
+  return (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
 
 }  // namespace tc
 }  // namespace rc

@@ -46,7 +46,8 @@ def main():
                       ("ours_tf32_build_fp32_volume", partial(R.CorrBlock, storage="fp32", math="tf32")),
                       ("ours_fp32", partial(R.CorrBlock, storage="fp32", math="fp32")),
                       ("ours_on_the_fly", R.AlternateCorrBlock),
-                      ("ours_on_the_fly_tensor_core", partial(R.AlternateCorrBlock, math="bf16"))):
+                      ("ours_on_the_fly_tensor_core", partial(R.AlternateCorrBlock, math="bf16")),
+                      ("ours_on_the_fly_tensor_core_fp16_operands", partial(R.AlternateCorrBlock, math="fp16"))):
         ms, up = timeit(cls, 5)
         epe = torch.sqrt(((up - up_ref) ** 2).sum(1)).mean().item()
         res[name] = {"ms": ms, "pairs_per_s": 1e3 * B / ms, "mean_epe_delta_px": epe}

@@ -528,6 +528,26 @@ def test_video_shape_beyond_32bit_offsets():
     assert torch.isfinite(got[-1, :, -1, -1]).all() and got[-1, :, -1, -1].abs().sum() > 0
 
 
+def test_alternate_tensor_core_fp16_operands():
+    """AlternateCorrBlock(math="fp16"): the same kernels with IEEE-half operands.  Against the fp32 block fed
+    fp16-rounded features level 0 differs by fp32 summation order only; against the unrounded fp32 block the whole
+    output is within 1e-3 (bf16 operands: 1e-2)."""
+    for shape in ((2, 128, 19, 45, 3), (1, 256, 55, 128, 4)):
+        B, D, H, W, r = shape
+        rng = np.random.default_rng(D + H)
+        f1 = rng.standard_normal((B, D, H, W)).astype(np.float32)
+        f2 = rng.standard_normal((B, D, H, W)).astype(np.float32)
+        coords = (O.coords_grid(B, H, W) + rng.normal(0, 4, (B, 2, H, W))).astype(np.float32)
+        got = R.AlternateCorrBlock(t(f1), t(f2), 4, r, math="fp16")(t(coords)).cpu().numpy()
+        n = (2 * r + 1) ** 2
+        ref16 = R.AlternateCorrBlock(t(fp16_round(f1)), t(fp16_round(f2)), 4, r)(t(coords)).cpu().numpy()
+        rel_close(got[:, :n], ref16[:, :n], 2e-5, f"alt fp16 operands {shape} level 0")
+        ref = R.AlternateCorrBlock(t(f1), t(f2), 4, r)(t(coords)).cpu().numpy()
+        rel_close(got, ref, 1e-3, f"alt fp16 operands {shape} vs fp32", floor=bf16_floor(f1, f2))
+    with pytest.raises(RuntimeError):
+        R.AlternateCorrBlock(t(f1), t(f2), 4, 4, math="fp8")
+
+
 # ------------------------------------------------------------------ on-the-fly path on the tensor cores
 @pytest.mark.parametrize("kind", ["smooth", "rand", "int", "far", "edge"])
 @pytest.mark.parametrize("shape", [(1, 64, 24, 40, 4), (2, 128, 19, 45, 3), (1, 256, 55, 128, 4),
