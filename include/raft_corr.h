@@ -46,6 +46,7 @@ extern "C" {
 #define RC_MATH_F32 0    /* CUDA-core fp32 FMA: what the reference's SGEMM does */
 #define RC_MATH_BF16 1   /* tcgen05 kind::f16, bf16 operands, fp32 accumulate in TMEM */
 #define RC_MATH_TF32 2   /* tcgen05 kind::tf32: the fp32 features rounded to tf32 (10 mantissa bits), fp32 accumulate */
+#define RC_MATH_F16 3    /* tcgen05 kind::f16 on IEEE-half operands (10 mantissa bits, range +-65 504), fp32 accumulate */
 
 typedef struct CUstream_st *rc_stream_t;   /* == cudaStream_t */
 

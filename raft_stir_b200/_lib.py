@@ -7,7 +7,7 @@ import os
 
 RC_MAX_LEVELS = 6
 RC_VOL_F32, RC_VOL_BF16, RC_VOL_F16 = 0, 1, 2
-RC_MATH_F32, RC_MATH_BF16, RC_MATH_TF32 = 0, 1, 2
+RC_MATH_F32, RC_MATH_BF16, RC_MATH_TF32, RC_MATH_F16 = 0, 1, 2, 3
 RC_ABI_VERSION = 3
 RC_STATIC_SCRATCH_BYTES = 16 << 20
 

@@ -24,7 +24,7 @@ from . import _lib
 from ._lib import RaftCorrError, check
 
 _STORAGE = {"bf16": _lib.RC_VOL_BF16, "fp32": _lib.RC_VOL_F32, "fp16": _lib.RC_VOL_F16}
-_MATH = {"bf16": _lib.RC_MATH_BF16, "fp32": _lib.RC_MATH_F32, "tf32": _lib.RC_MATH_TF32}
+_MATH = {"bf16": _lib.RC_MATH_BF16, "fp32": _lib.RC_MATH_F32, "tf32": _lib.RC_MATH_TF32, "fp16": _lib.RC_MATH_F16}
 _TORCH_DT = {_lib.RC_VOL_BF16: torch.bfloat16, _lib.RC_VOL_F32: torch.float32, _lib.RC_VOL_F16: torch.float16}
 
 
@@ -120,9 +120,10 @@ class CorrBlock:
              as bf16 and keeps three more mantissa bits; its range ends at 65 504, which correlations of
              normalised features (the encoder ends in instance norm) stay far below.  With math="tf32" it is the
              near-fp32 setting at the default's speed.
-    math:    "bf16" (default; tcgen05 tensor cores, fp32 accumulate), "tf32" (tensor cores on the fp32 features
-             rounded to tf32: 10 mantissa bits instead of 7, meant for storage="fp32") or "fp32" (CUDA-core fp32
-             FMA, the reference's SGEMM arithmetic).
+    math:    "bf16" (default; tcgen05 tensor cores, fp32 accumulate), "fp16" (the same at the same speed on
+             IEEE-half operands: 10 mantissa bits instead of 7, features beyond +-65 504 saturate), "tf32" (tensor
+             cores on the fp32 features rounded to tf32; half the MMA rate, twice the operand bytes) or "fp32"
+             (CUDA-core fp32 FMA, the reference's SGEMM arithmetic).
     out_dtype: torch.float32 (default, the reference's) or torch.float16 -- element type of what the call returns.
              fp16 is for inference under fp16 autocast (--mixed_precision): the update block's first convolution
              would cast the fp32 result itself; the lookup then writes half the bytes and the cast pass disappears.
@@ -141,7 +142,7 @@ class CorrBlock:
         storage = storage or os.environ.get("RAFT_CORR_STORAGE", "bf16")
         math = math or os.environ.get("RAFT_CORR_MATH", "bf16")
         if storage not in _STORAGE or math not in _MATH:
-            raise RaftCorrError(f"storage={storage!r} math={math!r}: expected storage bf16|fp16|fp32, math bf16|tf32|fp32")
+            raise RaftCorrError(f"storage={storage!r} math={math!r}: expected storage bf16|fp16|fp32, math bf16|fp16|tf32|fp32")
         self.vol_dtype = _STORAGE[storage]
         self.math = _MATH[math]
         _lib.lib()   # fail loudly before touching tensors if the extension is missing

@@ -120,7 +120,7 @@ int rc_pyramid_layout(int B, int H, int W, int num_levels, int vol_dtype, rc_lay
 int64_t rc_build_workspace_bytes(int B, int D, int H, int W, int math) {
   if (math == RC_MATH_F32) return 0;
   if (B < 1 || D < 1 || H < 1 || W < 1) return RC_EINVAL;
-  const int64_t es = math == RC_MATH_BF16 ? 2 : 4;
+  const int64_t es = (math == RC_MATH_BF16 || math == RC_MATH_F16) ? 2 : 4;
   const int64_t a = round_up64((int64_t)B * H * W * D * es, 1024);
   const int64_t b = round_up64((int64_t)B * packed_rows2(H, W) * D * es, 1024);
   return a + b;
@@ -131,7 +131,7 @@ int rc_build_pyramid(const float *fmap1, const float *fmap2, int B, int D, int H
                      rc_stream_t stream) {
   RC_REQUIRE(fmap1 && fmap2 && pyramid, "rc_build_pyramid: NULL pointer");
   RC_REQUIRE(D >= 1, "rc_build_pyramid: D=%d", D);
-  RC_REQUIRE(math == RC_MATH_F32 || math == RC_MATH_BF16 || math == RC_MATH_TF32, "unknown math %d", math);
+  RC_REQUIRE(math == RC_MATH_F32 || math == RC_MATH_BF16 || math == RC_MATH_TF32 || math == RC_MATH_F16, "unknown math %d", math);
   rc_layout lay;
   int r = make_layout(B, H, W, num_levels, vol_dtype, &lay);
   if (r) return r;
@@ -144,7 +144,7 @@ int rc_build_pyramid(const float *fmap1, const float *fmap2, int B, int D, int H
   }
   RC_REQUIRE(((uintptr_t)workspace & 255) == 0, "workspace must be 256-byte aligned");
   RC_REQUIRE(((uintptr_t)pyramid & 255) == 0, "pyramid must be 256-byte aligned");
-  const int64_t es = math == RC_MATH_BF16 ? 2 : 4;
+  const int64_t es = (math == RC_MATH_BF16 || math == RC_MATH_F16) ? 2 : 4;
   void *f1p = workspace;
   void *f2p = (char *)workspace + round_up64((int64_t)B * H * W * D * es, 1024);
   r = launch_pack(fmap1, fmap2, B, D, H, W, math, f1p, f2p, s);

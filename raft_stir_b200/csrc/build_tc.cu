@@ -49,6 +49,7 @@ constexpr int GW = TB_W / 2;           // block columns per epilogue group (16)
 struct TcParams {
   int B, N, MT, NT, nbx, KB, num_levels, stages;
   int group_pairs, num_groups;      // pairs processed together (see TileWalk)
+  uint32_t idesc;                   // instruction descriptor (operand format: bf16, f16 or tf32)
   float scale;                      // what is left of 1/sqrt(D) after the pack's exact power-of-two part
   // pyramid geometry (levels >= num_levels are unused)
   int Hl[4], Wl[4], tiles_y[4], tiles_x[4];
@@ -103,6 +104,8 @@ using namespace tc;
 // kind::f16: D = F32 (bit 4), A = B = BF16 (bits 7, 10), both K-major, N>>3 at 17, M>>4 at 24
 constexpr uint32_t IDESC_BF16 = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) |
                                 ((uint32_t)(BM >> 4) << 24);
+// kind::f16 with IEEE-half operands: format code 0
+constexpr uint32_t IDESC_F16 = (1u << 4) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
 // kind::tf32: the same with A = B = TF32 (format code 2)
 constexpr uint32_t IDESC_TF32 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) |
                                 ((uint32_t)(BM >> 4) << 24);
@@ -297,9 +300,9 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
             if (TF32)
               umma_tf32(d_tmem, desc_make(al + k * ((UMMA_K * 2) >> 4)), desc_make(bl + k * ((UMMA_K * 2) >> 4)),
                         IDESC_TF32, (kb | k) != 0);
-            else
+            else      // kind::f16: bf16 or IEEE-half operands, told apart by the descriptor's format fields
               umma_bf16(d_tmem, desc_make(al + k * ((UMMA_K * 2) >> 4)), desc_make(bl + k * ((UMMA_K * 2) >> 4)),
-                        IDESC_BF16, (kb | k) != 0);
+                        p.idesc, (kb | k) != 0);
           }
           umma_commit(bar_b_empty + 8 * st);   // frees the B stage when these MMAs retire
           if (++st == (uint32_t)p.stages) { st = 0; ph ^= 1; }
@@ -536,7 +539,7 @@ int encode(CUtensorMap *map, CUtensorMapDataType dt, int rank, const void *base,
 
 template <typename VolT, bool TF32>
 int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, const rc_layout &lay,
-               VolT *pyr, cudaStream_t s) {
+               VolT *pyr, bool half_operands, cudaStream_t s) {
   constexpr int BKE = TF32 ? BK / 2 : BK;
   constexpr int OPB = TF32 ? 4 : 2;                 // operand bytes per element
   constexpr size_t SLOT = TF32 ? A_KB_BYTES + B_ST_BYTES : B_ST_BYTES;
@@ -557,6 +560,9 @@ int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, con
   p.nbx = ceil_div(W, TB_W);
   p.NT = p.nbx * ceil_div(H, TB_H);
   p.KB = ceil_div(D, BKE);
+  p.idesc = TF32 ? IDESC_TF32 : half_operands ? IDESC_F16 : IDESC_BF16;
+  const CUtensorMapDataType op_type = TF32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
+                                      : half_operands ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
   p.num_levels = L;
   float pre_scale = 1.f;
   split_scale(D, &pre_scale, &p.scale);      // pre_scale was applied to fmap1 by the pack
@@ -602,16 +608,14 @@ int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, con
     cuuint64_t dims[3] = {(cuuint64_t)D, (cuuint64_t)N, (cuuint64_t)B};
     cuuint64_t str[2] = {(cuuint64_t)D * OPB, (cuuint64_t)N * D * OPB};
     cuuint32_t box[3] = {BKE, BM, 1};
-    int r = encode(&ma, TF32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, f1p, dims, str, box,
-                   CU_TENSOR_MAP_SWIZZLE_128B, "fmap1");
+    int r = encode(&ma, op_type, 3, f1p, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B, "fmap1");
     if (r) return r;
   }
   {
     cuuint64_t dims[3] = {(cuuint64_t)D, (cuuint64_t)rows2, (cuuint64_t)B};
     cuuint64_t str[2] = {(cuuint64_t)D * OPB, (cuuint64_t)rows2 * D * OPB};
     cuuint32_t box[3] = {BKE, BN, 1};
-    int r = encode(&mb, TF32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, f2p, dims, str, box,
-                   CU_TENSOR_MAP_SWIZZLE_128B, "fmap2");
+    int r = encode(&mb, op_type, 3, f2p, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B, "fmap2");
     if (r) return r;
   }
 
@@ -629,16 +633,17 @@ int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, con
 int launch_build_tc(const void *f1p, const void *f2p, int B, int D, int H, int W, const rc_layout &lay,
                     int vol_dtype, int math, void *pyramid, cudaStream_t s) {
   if (math == RC_MATH_TF32)
-    return vol_dtype == RC_VOL_BF16  ? build_tc_t<__nv_bfloat16, true>(f1p, f2p, B, D, H, W, lay, (__nv_bfloat16 *)pyramid, s)
-           : vol_dtype == RC_VOL_F16 ? build_tc_t<__half, true>(f1p, f2p, B, D, H, W, lay, (__half *)pyramid, s)
-                                     : build_tc_t<float, true>(f1p, f2p, B, D, H, W, lay, (float *)pyramid, s);
-  if (math != RC_MATH_BF16) {
+    return vol_dtype == RC_VOL_BF16  ? build_tc_t<__nv_bfloat16, true>(f1p, f2p, B, D, H, W, lay, (__nv_bfloat16 *)pyramid, false, s)
+           : vol_dtype == RC_VOL_F16 ? build_tc_t<__half, true>(f1p, f2p, B, D, H, W, lay, (__half *)pyramid, false, s)
+                                     : build_tc_t<float, true>(f1p, f2p, B, D, H, W, lay, (float *)pyramid, false, s);
+  if (math != RC_MATH_BF16 && math != RC_MATH_F16) {
     set_error("tensor-core build: math=%d is not a tensor-core mode", math);
     return RC_EINVAL;
   }
-  return vol_dtype == RC_VOL_BF16  ? build_tc_t<__nv_bfloat16, false>(f1p, f2p, B, D, H, W, lay, (__nv_bfloat16 *)pyramid, s)
-         : vol_dtype == RC_VOL_F16 ? build_tc_t<__half, false>(f1p, f2p, B, D, H, W, lay, (__half *)pyramid, s)
-                                   : build_tc_t<float, false>(f1p, f2p, B, D, H, W, lay, (float *)pyramid, s);
+  const bool half = math == RC_MATH_F16;
+  return vol_dtype == RC_VOL_BF16  ? build_tc_t<__nv_bfloat16, false>(f1p, f2p, B, D, H, W, lay, (__nv_bfloat16 *)pyramid, half, s)
+         : vol_dtype == RC_VOL_F16 ? build_tc_t<__half, false>(f1p, f2p, B, D, H, W, lay, (__half *)pyramid, half, s)
+                                   : build_tc_t<float, false>(f1p, f2p, B, D, H, W, lay, (float *)pyramid, half, s);
 }
 
 }  // namespace rc

@@ -27,6 +27,10 @@ template <>
 __device__ __forceinline__ void store_pair<__nv_bfloat16>(__nv_bfloat16 *p, float a, float b) {
   *reinterpret_cast<__nv_bfloat162 *>(p) = __floats2bfloat162_rn(a, b);
 }
+template <>
+__device__ __forceinline__ void store_pair<__half>(__half *p, float a, float b) {
+  *reinterpret_cast<uint32_t *>(p) = pack2<__half>(a, b);     // saturating
+}
 // fp32 operands feed kind::tf32, which reads the top 19 bits and ignores the rest (truncation): round to nearest here
 __device__ __forceinline__ float round_tf32(float v) {
   uint32_t r;
@@ -103,6 +107,9 @@ int launch_pack(const float *fmap1, const float *fmap2, int B, int D, int H, int
   if (math == RC_MATH_BF16) {
     pack_features_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>(
         fmap1, fmap2, (__nv_bfloat16 *)f1p, (__nv_bfloat16 *)f2p, D, H, W, groups1, nbx, rows2, pre);
+  } else if (math == RC_MATH_F16) {
+    pack_features_kernel<__half><<<grid, 256, 0, s>>>(fmap1, fmap2, (__half *)f1p, (__half *)f2p, D, H, W, groups1,
+                                                       nbx, rows2, pre);
   } else {
     pack_features_kernel<float><<<grid, 256, 0, s>>>(fmap1, fmap2, (float *)f1p, (float *)f2p, D, H,
                                                      W, groups1, nbx, rows2, pre);

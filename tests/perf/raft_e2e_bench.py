@@ -42,6 +42,7 @@ def main():
     res["torch_corrblock_on_gpu"] = {"ms": ms_ref, "pairs_per_s": 1e3 * B / ms_ref}
     for name, cls in (("ours_bf16_tensor_core", R.CorrBlock),
                       ("ours_bf16_build_fp16_volume", partial(R.CorrBlock, storage="fp16", math="bf16")),
+                      ("ours_fp16_build_fp16_volume", partial(R.CorrBlock, storage="fp16", math="fp16")),
                       ("ours_tf32_build_fp16_volume", partial(R.CorrBlock, storage="fp16", math="tf32")),
                       ("ours_tf32_build_fp32_volume", partial(R.CorrBlock, storage="fp32", math="tf32")),
                       ("ours_fp32", partial(R.CorrBlock, storage="fp32", math="fp32")),

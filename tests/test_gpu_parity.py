@@ -114,7 +114,7 @@ def fp16_round(a):
     return np.asarray(a, np.float32).astype(np.float16).astype(np.float32)
 
 
-@pytest.mark.parametrize("math", ["bf16", "tf32", "fp32"])
+@pytest.mark.parametrize("math", ["bf16", "fp16", "tf32", "fp32"])
 @pytest.mark.parametrize("shape", [(1, 256, 55, 128), (2, 128, 19, 45), (3, 32, 8, 9)])
 def test_fp16_storage_build_and_lookup(shape, math):
     """storage="fp16" (RC_VOL_F16): every level equals the oracle's value (for the operands that math sees) rounded
@@ -127,7 +127,7 @@ def test_fp16_storage_build_and_lookup(shape, math):
     L = 4 if min(H, W) >= 8 else 3
     blk = R.CorrBlock(t(f1), t(f2), L, 4, storage="fp16", math=math)
     assert blk._buf.dtype == torch.float16
-    rnd = {"bf16": bf16_round, "tf32": tf32_round, "fp32": lambda a: a}[math]
+    rnd = {"bf16": bf16_round, "fp16": fp16_round, "tf32": tf32_round, "fp32": lambda a: a}[math]
     pyr = O.corr_pyramid(rnd(f1).astype(np.float64), rnd(f2).astype(np.float64), L)
     got = [v[:, 0].float().cpu().numpy() for v in blk.corr_pyramid]
     for l in range(L):
@@ -169,7 +169,7 @@ def test_build_tensor_core_vs_oracle_shapes(shape, storage):
                   floor=bf16_floor(f1, f2))
 
 
-@pytest.mark.parametrize("math", ["bf16", "tf32", "fp32"])
+@pytest.mark.parametrize("math", ["bf16", "fp16", "tf32", "fp32"])
 @pytest.mark.parametrize("storage", ["bf16", "fp16", "fp32"])
 def test_padding_columns_of_edge_tiles_are_zero(storage, math):
     """rc_layout's invariant: inside rows < H_l, tile columns >= W_l hold zeros

@@ -1,5 +1,5 @@
 #!/usr/bin/env python3
-"""Randomised stress of the tensor-core volume build (bf16 and tf32 operands, all three storage types) against the
+"""Randomised stress of the tensor-core volume build (bf16, fp16 and tf32 operands, all three storage types) against the
 CUDA-core fp32 build of the same library on operand-rounded features, plus a lookup on each: random batch, channel
 count, map size and number of levels, ITER cases (default 200).  One JSON line; exits 1 on any mismatch."""
 import json
@@ -30,12 +30,13 @@ with torch.no_grad():
         H = int(rng.integers(8, 64))
         W = int(rng.integers(8, 90))
         L = int(rng.choice([1, 2, 3, 4]))
-        math = ["bf16", "tf32"][it % 2]
-        storage = ["fp32", "bf16", "fp16"][(it // 2) % 3]
+        math = ["bf16", "tf32", "fp16"][it % 3]
+        storage = ["fp32", "bf16", "fp16"][(it // 3) % 3]
         g = torch.Generator().manual_seed(1000 + it)
         f1 = torch.randn(B, D, H, W, generator=g).to(dev)
         f2 = torch.randn(B, D, H, W, generator=g).to(dev)
-        r1, r2 = (f1.bfloat16().float(), f2.bfloat16().float()) if math == "bf16" else (tf32_round(f1), tf32_round(f2))
+        r1, r2 = {"bf16": (f1.bfloat16().float(), f2.bfloat16().float()), "fp16": (f1.half().float(), f2.half().float()),
+                  "tf32": (tf32_round(f1), tf32_round(f2))}[math]
         ref = R.CorrBlock(r1, r2, L, 4, storage="fp32", math="fp32")
         blk = R.CorrBlock(f1, f2, L, 4, storage=storage, math=math)
         tol = {"fp32": 2e-5, "bf16": 2.0 ** -8, "fp16": 2.0 ** -11 * 1.01}[storage]
