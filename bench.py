@@ -189,7 +189,8 @@ def main():
     ap.add_argument("--batch", type=int, default=64,
                     help="frame pairs per GPU per step (BASELINE configs[2]: batch 64 Sintel-shape pairs)")
     ap.add_argument("--e2e-batch", type=int, default=16, help="frame pairs per end-to-end step (host buffers are pinned)")
-    ap.add_argument("--storage", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--storage", default="bf16", choices=["bf16", "fp16", "fp32"])
+    ap.add_argument("--math", default="bf16", choices=["bf16", "fp16", "tf32"], help="operand type of the tensor-core build")
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU baseline work")
     ap.add_argument("--no-extras", action="store_true")
@@ -220,12 +221,12 @@ def main():
     B = args.batch
     f1, f2, coords = make_inputs(B, device, seed=1000 + rank)
     stream = torch.cuda.current_stream()
-    es = 2 if args.storage == "bf16" else 4
+    es = 4 if args.storage == "fp32" else 2
 
     def step(rec=None):
         if rec is not None:
             rec.append(torch.cuda.Event(enable_timing=True)); rec[-1].record(stream)
-        blk = R.CorrBlock(f1, f2, LEVELS, RADIUS, storage=args.storage)
+        blk = R.CorrBlock(f1, f2, LEVELS, RADIUS, storage=args.storage, math=args.math)
         if rec is not None:
             rec.append(torch.cuda.Event(enable_timing=True)); rec[-1].record(stream)
         out = None
@@ -319,7 +320,7 @@ def main():
         def e2e_step():
             d1 = hf1.to(device, non_blocking=True)
             d2 = hf2.to(device, non_blocking=True)
-            blk = R.CorrBlock(d1, d2, LEVELS, RADIUS, storage=args.storage)
+            blk = R.CorrBlock(d1, d2, LEVELS, RADIUS, storage=args.storage, math=args.math)
             for i in range(ITERS):
                 c = hcoords[i].to(device, non_blocking=True)
                 o = blk(c)
@@ -368,10 +369,10 @@ def main():
             "metric": "frame_pairs_per_s_corr_hot_path_55x128x256_12iters",
             "value": world * B * args.steps / (ms * 1e-3), "unit": "pairs/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "bf16" if args.storage == "bf16" else "f32",
+            "scaling": "weak", "vs_baseline": None, "dtype": {"bf16": "bf16", "fp16": "f16", "tf32": "tf32"}[args.math],
             "data": "synthetic",
             "config": {"workload": WORKLOAD, "pairs_per_gpu_per_step": B, "volume_storage": args.storage,
-                       "build_math": "bf16 tcgen05, fp32 accumulate", "l2": "working set per step (pyramid %.0f MB) exceeds the 126 MB L2" % (B * PYR_ELEMS * es / 1e6),
+                       "build_math": f"{args.math} tcgen05, fp32 accumulate", "l2": "working set per step (pyramid %.0f MB) exceeds the 126 MB L2" % (B * PYR_ELEMS * es / 1e6),
                        "parallelism": f"pairs sharded over {world} rank(s), no collective"},
             "roofline": roof, "kernels": kernels, "cpu_baseline": cpu, "e2e": e2e,
             "gpu_launches": world * args.steps * (2 + ITERS), "clocks": clocks, "extras": extras,
@@ -399,8 +400,8 @@ def run_extras(R, device, args, pk):
     try:
         with torch.no_grad():
             f1, f2, coords = make_inputs(1, device, seed=7)
-            out["b1_build_ms"] = timeit(lambda: R.CorrBlock(f1, f2, LEVELS, RADIUS, storage=args.storage), 20)
-            blk = R.CorrBlock(f1, f2, LEVELS, RADIUS, storage=args.storage)
+            out["b1_build_ms"] = timeit(lambda: R.CorrBlock(f1, f2, LEVELS, RADIUS, storage=args.storage, math=args.math), 20)
+            blk = R.CorrBlock(f1, f2, LEVELS, RADIUS, storage=args.storage, math=args.math)
             out["b1_lookup_ms"] = timeit(lambda: blk(coords[0]), 50)
             out["b1_build_fp32_simt_ms"] = timeit(lambda: R.CorrBlock(f1, f2, LEVELS, RADIUS, storage="fp32", math="fp32"), 3)
             out["b1_build_tf32_fp32_storage_ms"] = timeit(lambda: R.CorrBlock(f1, f2, LEVELS, RADIUS, storage="fp32", math="tf32"), 10)
@@ -418,13 +419,13 @@ def run_extras(R, device, args, pk):
 
         def train_step():
             a1.grad = None; a2.grad = None
-            blk = R.CorrBlock(a1, a2, LEVELS, RADIUS, storage=args.storage)
+            blk = R.CorrBlock(a1, a2, LEVELS, RADIUS, storage=args.storage, math=args.math)
             loss = sum(blk(c).sum() for c in cc)
             loss.backward()
         out["chairs_b10_fwd_bwd_ms"] = timeit(train_step, 5)
         # the two backward kernels alone, same shape: 12 lookup backwards into one gradient pyramid, then the build backward
         with torch.no_grad():
-            blk = R.CorrBlock(a1.detach(), a2.detach(), LEVELS, RADIUS, storage=args.storage)
+            blk = R.CorrBlock(a1.detach(), a2.detach(), LEVELS, RADIUS, storage=args.storage, math=args.math)
             go = torch.randn(Bc, LEVELS * (2 * RADIUS + 1) ** 2, Hc, Wc, device=device)
             blk._lookup_backward(cc[0], go, True, False)
             ms = timeit(lambda: blk._lookup_backward(cc[0], go, True, False), 20)
@@ -440,8 +441,8 @@ def run_extras(R, device, args, pk):
             v1 = torch.randn(1, D, Hv, Wv, generator=g).to(device)
             v2 = torch.randn(1, D, Hv, Wv, generator=g).to(device)
             cv = R.coords_grid(1, Hv, Wv, device) + 5 * torch.randn(1, 2, Hv, Wv, device=device)
-            out["v1080_build_ms"] = timeit(lambda: R.CorrBlock(v1, v2, LEVELS, RADIUS, storage=args.storage), 3)
-            blk = R.CorrBlock(v1, v2, LEVELS, RADIUS, storage=args.storage)
+            out["v1080_build_ms"] = timeit(lambda: R.CorrBlock(v1, v2, LEVELS, RADIUS, storage=args.storage, math=args.math), 3)
+            blk = R.CorrBlock(v1, v2, LEVELS, RADIUS, storage=args.storage, math=args.math)
             out["v1080_lookup_ms"] = timeit(lambda: blk(cv), 20)
             del blk
             altv = R.AlternateCorrBlock(v1, v2, LEVELS, RADIUS)
@@ -454,11 +455,11 @@ def run_extras(R, device, args, pk):
             f1b = torch.randn(args.batch, D, H, W, device=device)
             f2b = torch.randn(args.batch, D, H, W, device=device)
             cb = R.coords_grid(args.batch, H, W, device) + 5 * torch.randn(args.batch, 2, H, W, device=device)
-            blk16 = R.CorrBlock(f1b, f2b, LEVELS, RADIUS, storage=args.storage, out_dtype=torch.float16)
+            blk16 = R.CorrBlock(f1b, f2b, LEVELS, RADIUS, storage=args.storage, math=args.math, out_dtype=torch.float16)
             del f1b, f2b
             ms = timeit(lambda: blk16(cb), 20)
             nq = args.batch * H * W
-            b16 = nq * (LEVELS * (2 * RADIUS + 2) ** 2 * (2 if args.storage == "bf16" else 4) + 8
+            b16 = nq * (LEVELS * (2 * RADIUS + 2) ** 2 * (4 if args.storage == "fp32" else 2) + 8
                         + LEVELS * (2 * RADIUS + 1) ** 2 * 2)
             out["lookup_fp16_out_ms"] = ms
             out["lookup_fp16_out_GB/s"] = b16 / (ms * 1e-3) / 1e9
