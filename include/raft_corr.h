@@ -248,6 +248,9 @@ RC_API int rc_alt_lookup_fwd_tc(const void *fmap1_16, const void *fmap2_pyr_16, 
  */
 RC_API int rc_upsample_flow(const float *flow, const float *mask, int B, int H, int W, float *out,
                      rc_stream_t stream);
+/* the same reading the mask as IEEE half [B, 576, H, W], as fp16 autocast leaves it (softmax still in fp32) */
+RC_API int rc_upsample_flow_f16mask(const float *flow, const void *mask_f16, int B, int H, int W, float *out,
+                             rc_stream_t stream);
 RC_API int rc_upsample_flow_bwd(const float *flow, const float *mask, const float *gout, int B, int H, int W,
                          float *dflow, float *dmask, rc_stream_t stream);
 RC_API int rc_upflow8(const float *flow, int B, int C, int H, int W, float *out, rc_stream_t stream);

@@ -49,6 +49,7 @@ SIGNATURES = {
     "rc_alt_lookup_fwd_tc": (_i, [_p, _p, _i, _p, _i, _i, _i, _i, _i, _i, _p, _p]),
     "rc_lookup_fwd_f16": (_i, [_p, _i, _p, _i, _i, _i, _i, _i, _p, _p]),
     "rc_upsample_flow": (_i, [_p, _p, _i, _i, _i, _p, _p]),
+    "rc_upsample_flow_f16mask": (_i, [_p, _p, _i, _i, _i, _p, _p]),
     "rc_upsample_flow_bwd": (_i, [_p, _p, _p, _i, _i, _i, _p, _p, _p]),
     "rc_upflow8": (_i, [_p, _i, _i, _i, _i, _p, _p]),
     "rc_upflow8_bwd": (_i, [_p, _i, _i, _i, _i, _p, _p]),

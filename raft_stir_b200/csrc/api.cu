@@ -35,7 +35,8 @@ int launch_alt_lookup_tc(const void *f1_bf16, const void *f2_pyr_bf16, const flo
                          int W, int num_levels, int radius, const int64_t *off, int half_operands, float *out,
                          cudaStream_t s);
 // upsample.cu
-int launch_upsample_flow(const float *flow, const float *mask, int B, int H, int W, float *out, cudaStream_t s);
+int launch_upsample_flow(const float *flow, const void *mask, int mask_is_half, int B, int H, int W, float *out,
+                         cudaStream_t s);
 int launch_upsample_flow_bwd(const float *flow, const float *mask, const float *gout, int B, int H, int W,
                              float *dflow, float *dmask, cudaStream_t s);
 int launch_upflow8(const float *flow, int B, int C, int H, int W, float *out, cudaStream_t s);
@@ -322,7 +323,14 @@ int rc_alt_lookup_fwd_tc(const void *fmap1_bf16, const void *fmap2_pyr_bf16, int
 int rc_upsample_flow(const float *flow, const float *mask, int B, int H, int W, float *out, rc_stream_t stream) {
   RC_REQUIRE(flow && mask && out, "rc_upsample_flow: NULL pointer");
   RC_REQUIRE(B >= 1 && B <= 65535 && H >= 1 && H <= 65535 && W >= 1, "rc_upsample_flow: bad sizes B=%d H=%d W=%d", B, H, W);
-  return launch_upsample_flow(flow, mask, B, H, W, out, (cudaStream_t)stream);
+  return launch_upsample_flow(flow, mask, 0, B, H, W, out, (cudaStream_t)stream);
+}
+
+int rc_upsample_flow_f16mask(const float *flow, const void *mask_f16, int B, int H, int W, float *out,
+                             rc_stream_t stream) {
+  RC_REQUIRE(flow && mask_f16 && out, "rc_upsample_flow_f16mask: NULL pointer");
+  RC_REQUIRE(B >= 1 && B <= 65535 && H >= 1 && H <= 65535 && W >= 1, "rc_upsample_flow_f16mask: bad sizes B=%d H=%d W=%d", B, H, W);
+  return launch_upsample_flow(flow, mask_f16, 1, B, H, W, out, (cudaStream_t)stream);
 }
 
 int rc_upsample_flow_bwd(const float *flow, const float *mask, const float *gout, int B, int H, int W, float *dflow,

@@ -34,6 +34,17 @@ __device__ __forceinline__ void load_neighbours(const float *__restrict__ flow, 
     }
 }
 
+// mask element loads: fp32, or fp16 as fp16 autocast leaves the update block's output (core/raft.py:127-128)
+__device__ __forceinline__ float ld_mask(const float *p) { return __ldg(p); }
+__device__ __forceinline__ float ld_mask(const __half *p) { return __half2float(__ldg(p)); }
+__device__ __forceinline__ float4 ld_mask4(const float *p) { return __ldg(reinterpret_cast<const float4 *>(p)); }
+__device__ __forceinline__ float4 ld_mask4(const __half *p) {
+  const uint2 u = __ldg(reinterpret_cast<const uint2 *>(p));
+  const float2 a = __half22float2(*reinterpret_cast<const __half2 *>(&u.x));
+  const float2 b = __half22float2(*reinterpret_cast<const __half2 *>(&u.y));
+  return make_float4(a.x, a.y, b.x, b.y);
+}
+
 __device__ __forceinline__ float ex2_approx(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -54,8 +65,9 @@ __device__ __forceinline__ void softmax9(float (&m)[9]) {
   for (int k = 0; k < 9; ++k) m[k] *= inv;
 }
 
+template <typename MT>
 __global__ void __launch_bounds__(256)
-upsample_flow_kernel(const float *__restrict__ flow, const float *__restrict__ mask, float *__restrict__ out, int H,
+upsample_flow_kernel(const float *__restrict__ flow, const MT *__restrict__ mask, float *__restrict__ out, int H,
                      int W) {
   __shared__ float tile[2][8][UP_ROW];
   const int lane = threadIdx.x & 31, sx = threadIdx.x >> 5;
@@ -65,12 +77,12 @@ upsample_flow_kernel(const float *__restrict__ flow, const float *__restrict__ m
   const size_t HW = (size_t)H * W;
   float nb[2][9];
   load_neighbours(flow, b, y, x, H, W, in, nb);
-  const float *mp = mask + (size_t)b * 576 * HW + (size_t)y * W + (in ? x : 0);
+  const MT *mp = mask + (size_t)b * 576 * HW + (size_t)y * W + (in ? x : 0);
 #pragma unroll 2
   for (int sy = 0; sy < 8; ++sy) {
     float m[9];
 #pragma unroll
-    for (int k = 0; k < 9; ++k) m[k] = in ? __ldg(mp + (size_t)(k * 64 + sy * 8 + sx) * HW) : 0.f;
+    for (int k = 0; k < 9; ++k) m[k] = in ? ld_mask(mp + (size_t)(k * 64 + sy * 8 + sx) * HW) : 0.f;
     softmax9(m);
     float o0 = 0.f, o1 = 0.f;
 #pragma unroll
@@ -102,8 +114,9 @@ upsample_flow_kernel(const float *__restrict__ flow, const float *__restrict__ m
 // enough bytes in flight to keep HBM busy while the other CTA computes and stores.
 constexpr int UPV_ROW = 8 * UP_TX + 5 * 8;   // skew 5 per 32 positions
 
+template <typename MT>
 __global__ void __launch_bounds__(512, 2)
-upsample_flow_v4_kernel(const float *__restrict__ flow, const float *__restrict__ mask, float *__restrict__ out,
+upsample_flow_v4_kernel(const float *__restrict__ flow, const MT *__restrict__ mask, float *__restrict__ out,
                         int H, int W) {
   __shared__ float tile[2][8][UPV_ROW];
   __shared__ float fl[2][3][UP_TX + 4];       // 8*flow at rows y-1..y+1, columns x0-1..x0+32 (index 0 = x0-1)
@@ -114,11 +127,10 @@ upsample_flow_v4_kernel(const float *__restrict__ flow, const float *__restrict_
   const bool in = x0 + 4 * q < W;              // W % 4 == 0: a quad is inside or outside as a whole
   float4 m[9];
   {
-    const float *mp = mask + (size_t)b * 576 * HW + (size_t)y * W + x0 + 4 * q;
+    const MT *mp = mask + (size_t)b * 576 * HW + (size_t)y * W + x0 + 4 * q;
 #pragma unroll
     for (int k = 0; k < 9; ++k)
-      m[k] = in ? __ldg(reinterpret_cast<const float4 *>(mp + (size_t)(k * 64 + sy * 8 + sx) * HW))
-                : make_float4(0.f, 0.f, 0.f, 0.f);
+      m[k] = in ? ld_mask4(mp + (size_t)(k * 64 + sy * 8 + sx) * HW) : make_float4(0.f, 0.f, 0.f, 0.f);
   }
   if (t < 2 * 3 * (UP_TX + 2)) {
     const int c = t / (3 * (UP_TX + 2)), r = (t / (UP_TX + 2)) % 3, i = t % (UP_TX + 2);
@@ -273,16 +285,24 @@ upflow8_bwd_kernel(const float *__restrict__ gout, float *__restrict__ dflow, in
 
 }  // namespace
 
-int launch_upsample_flow(const float *flow, const float *mask, int B, int H, int W, float *out, cudaStream_t s) {
+template <typename MT>
+static int upsample_flow_t(const float *flow, const MT *mask, int B, int H, int W, float *out, cudaStream_t s) {
   dim3 grid(ceil_div(W, UP_TX), H, B);
-  if (W % 4 == 0 && ((uintptr_t)mask & 15) == 0) {
-    upsample_flow_v4_kernel<<<grid, 512, 0, s>>>(flow, mask, out, H, W);
+  // four pixels per load: 16 bytes of fp32, 8 of fp16; the plane stride H*W keeps that alignment when W % 4 == 0
+  if (W % 4 == 0 && ((uintptr_t)mask & (4 * sizeof(MT) - 1)) == 0) {
+    upsample_flow_v4_kernel<MT><<<grid, 512, 0, s>>>(flow, mask, out, H, W);
     RC_LAUNCH_CHECK("upsample_flow_v4_kernel");
     return RC_OK;
   }
-  upsample_flow_kernel<<<grid, 256, 0, s>>>(flow, mask, out, H, W);
+  upsample_flow_kernel<MT><<<grid, 256, 0, s>>>(flow, mask, out, H, W);
   RC_LAUNCH_CHECK("upsample_flow_kernel");
   return RC_OK;
+}
+
+int launch_upsample_flow(const float *flow, const void *mask, int mask_is_half, int B, int H, int W, float *out,
+                         cudaStream_t s) {
+  return mask_is_half ? upsample_flow_t<__half>(flow, (const __half *)mask, B, H, W, out, s)
+                      : upsample_flow_t<float>(flow, (const float *)mask, B, H, W, out, s);
 }
 
 int launch_upsample_flow_bwd(const float *flow, const float *mask, const float *gout, int B, int H, int W,

@@ -25,9 +25,9 @@ from .corr import _guard, _require_cuda_f32, _stream
 def _upsample_fwd(flow, mask):
     B, _, H, W = flow.shape
     out = torch.empty(B, 2, 8 * H, 8 * W, device=flow.device, dtype=torch.float32)
+    fn = _lib.lib().rc_upsample_flow_f16mask if mask.dtype is torch.float16 else _lib.lib().rc_upsample_flow
     with _guard(flow.device):
-        check(_lib.lib().rc_upsample_flow(flow.data_ptr(), mask.data_ptr(), B, H, W, out.data_ptr(), _stream(flow)),
-              "rc_upsample_flow")
+        check(fn(flow.data_ptr(), mask.data_ptr(), B, H, W, out.data_ptr(), _stream(flow)), "rc_upsample_flow")
     return out
 
 
@@ -77,12 +77,16 @@ def upsample_flow(flow: torch.Tensor, mask: torch.Tensor) -> torch.Tensor:
     [B, 576, H, W] output (any float dtype: autocast hands over fp16; it is read as fp32 like the reference's
     softmax does under autocast)."""
     flow = _require_cuda_f32(flow, "flow")
-    mask = _require_cuda_f32(mask, "mask")
+    grad = torch.is_grad_enabled() and (flow.requires_grad or (isinstance(mask, torch.Tensor) and mask.requires_grad))
+    if isinstance(mask, torch.Tensor) and mask.is_cuda and mask.dtype is torch.float16 and not grad:
+        mask = mask.contiguous()             # inference under fp16 autocast: read as it is, no fp32 copy
+    else:
+        mask = _require_cuda_f32(mask, "mask")
     if flow.dim() != 4 or flow.shape[1] != 2:
         raise RaftCorrError(f"flow must be [B,2,H,W], got {tuple(flow.shape)}")
     if mask.dim() != 4 or mask.shape[1] != 576 or mask.shape[0] != flow.shape[0] or mask.shape[2:] != flow.shape[2:]:
         raise RaftCorrError(f"mask must be [B,576,H,W] matching flow {tuple(flow.shape)}, got {tuple(mask.shape)}")
-    if torch.is_grad_enabled() and (flow.requires_grad or mask.requires_grad):
+    if grad:
         return _UpsampleFn.apply(flow, mask)
     return _upsample_fwd(flow, mask)          # inference: no autograd node to build
 

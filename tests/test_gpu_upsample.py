@@ -71,6 +71,25 @@ def test_upsample_flow_matches_oracle(shape):
     np.testing.assert_allclose(dmask.cpu().numpy(), rm, rtol=RTOL, atol=ATOL)
 
 
+@pytest.mark.parametrize("shape", [(2, 3, 31), (1, 7, 32), (1, 55, 128)])
+def test_upsample_flow_fp16_mask(shape):
+    """A half-precision mask (what fp16 autocast hands over) is read directly: same result as the fp32 kernel on the
+    mask converted by torch, bit for bit (the conversion to fp32 is exact and everything after it is the same code)."""
+    B, H, W = shape
+    rng = np.random.default_rng(W)
+    flow = t(rng.normal(0, 5, (B, 2, H, W)))
+    mask16 = t(rng.normal(0, 3, (B, 576, H, W))).half()
+    with torch.no_grad():
+        got = R.upsample_flow(flow, mask16)
+        want = R.upsample_flow(flow, mask16.float())
+    assert got.dtype == torch.float32 and torch.equal(got, want)
+    # with autograd the mask is taken through fp32 and gradients come back in fp32
+    m = mask16.float().requires_grad_(True)
+    up = R.upsample_flow(flow, m)
+    (dm,) = torch.autograd.grad(up, (m,), torch.ones_like(up))
+    assert dm.dtype == torch.float32 and torch.isfinite(dm).all()
+
+
 def test_upsample_flow_extreme_logits():
     """softmax with logits of +-80 (one neighbour takes all the weight) stays finite and picks that neighbour."""
     B, H, W = 1, 4, 6

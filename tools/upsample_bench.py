@@ -46,6 +46,9 @@ for name, (B, H, W) in {"sintel_b1": (1, 55, 128), "sintel_b64": (64, 55, 128), 
         err = (a - b).abs().max().item()
         ours = timeit(lambda: R.upsample_flow(flow, mask), 50)
         ref = timeit(lambda: ref_upsample(flow, mask), 20)
+        m16 = mask.half()
+        ours16 = timeit(lambda: R.upsample_flow(flow, m16), 50)
+        ref16 = timeit(lambda: ref_upsample(flow, m16), 20)       # what the reference does with autocast's fp16 mask
     fl, mk = flow.clone().requires_grad_(True), mask.clone().requires_grad_(True)
 
     def fb(fn):
@@ -54,5 +57,5 @@ for name, (B, H, W) in {"sintel_b1": (1, 55, 128), "sintel_b64": (64, 55, 128), 
     ours_fb, ref_fb = timeit(lambda: fb(R.upsample_flow), 20), timeit(lambda: fb(ref_upsample), 10)
     bytes_fwd = B * H * W * (576 * 4 + 2 * 4 + 128 * 4)
     res[name] = {"ours_ms": ours, "reference_torch_ms": ref, "speedup": ref / ours, "max_abs_diff": err,
-                 "ours_GB/s": bytes_fwd / ours / 1e6, "ours_fwd_bwd_ms": ours_fb, "reference_fwd_bwd_ms": ref_fb}
+                 "ours_GB/s": bytes_fwd / ours / 1e6, "ours_fp16_mask_ms": ours16, "reference_torch_fp16_mask_ms": ref16, "ours_fwd_bwd_ms": ours_fb, "reference_fwd_bwd_ms": ref_fb}
 print(json.dumps(res))
