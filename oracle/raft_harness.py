@@ -91,26 +91,33 @@ class TorchCorrBlock:
 
 
 @torch.no_grad()
-def raft_forward(nets, image1, image2, iters=12, corr_cls=TorchCorrBlock, last_only=True, upsample_fn=None):
-    """RAFT.forward(test_mode=True) (core/raft.py:86-144) -> (flow_low, flow_up)."""
+def raft_forward(nets, image1, image2, iters=12, corr_cls=TorchCorrBlock, last_only=True, upsample_fn=None,
+                 mixed_precision=False):
+    """RAFT.forward(test_mode=True) (core/raft.py:86-144) -> (flow_low, flow_up).  mixed_precision wraps the three
+    network calls in fp16 autocast exactly where the reference does (core/raft.py:98-100, :110-114, :127-128)."""
     fnet, cnet, update = nets
+    amp = lambda: torch.autocast("cuda", dtype=torch.float16, enabled=mixed_precision)   # noqa: E731
     image1 = (2 * (image1 / 255.0) - 1.0).contiguous()
     image2 = (2 * (image2 / 255.0) - 1.0).contiguous()
     B = image1.shape[0]
     # the reference feeds [image1, image2] as a list, which its encoder concatenates on the batch
     # axis and splits again (core/extractor.py:171-174, :189-190)
-    fmaps = fnet(torch.cat([image1, image2], dim=0)).float()
+    with amp():
+        fmaps = fnet(torch.cat([image1, image2], dim=0))
+    fmaps = fmaps.float()
     fmap1, fmap2 = fmaps[:B], fmaps[B:]
     corr_fn = corr_cls(fmap1, fmap2, radius=4)
-    net, inp = torch.split(cnet(image1), [HDIM, CDIM], dim=1)
-    net, inp = torch.tanh(net), torch.relu(inp)
+    with amp():
+        net, inp = torch.split(cnet(image1), [HDIM, CDIM], dim=1)
+        net, inp = torch.tanh(net), torch.relu(inp)
     H8, W8 = image1.shape[2] // 8, image1.shape[3] // 8
     coords0 = coords_grid(B, H8, W8, image1.device)
     coords1 = coords0.clone()
     flow_up = None
     for it in range(iters):
         corr = corr_fn(coords1)
-        net, up_mask, delta = update(net, inp, corr, coords1 - coords0)
+        with amp():
+            net, up_mask, delta = update(net, inp, corr, coords1 - coords0)
         coords1 = coords1 + delta
         if not last_only or it == iters - 1:
             flow_up = (upsample_fn or upsample_flow)(coords1 - coords0, up_mask)   # the reference: every iteration

@@ -60,6 +60,14 @@ def main():
     ms, up = timeit(R.CorrBlock, 5, last_only=False, upsample_fn=R.upsample_flow)
     res["ours_bf16_block_and_upsampling_every_iteration"] = {
         "ms": ms, "pairs_per_s": 1e3 * B / ms, "mean_epe_delta_px": torch.sqrt(((up - up_ref) ** 2).sum(1)).mean().item()}
+    # --mixed_precision: the three networks under fp16 autocast as the reference runs them; this library's block then
+    # answers in fp16 and the upsampling reads autocast's fp16 mask
+    ms, up16 = timeit(Hn.TorchCorrBlock, 5, mixed_precision=True)
+    res["mixed_precision_torch_corrblock"] = {"ms": ms, "pairs_per_s": 1e3 * B / ms,
+                                              "mean_epe_vs_fp32_px": torch.sqrt(((up16 - up_ref) ** 2).sum(1)).mean().item()}
+    ms, up = timeit(partial(R.CorrBlock, out_dtype=torch.float16), 5, mixed_precision=True, upsample_fn=R.upsample_flow)
+    res["mixed_precision_ours_fp16_out"] = {"ms": ms, "pairs_per_s": 1e3 * B / ms,
+                                            "mean_epe_vs_reference_mixed_px": torch.sqrt(((up - up16) ** 2).sum(1)).mean().item()}
     # the whole forward (encoders, volume build, 12 x (lookup + update block), upsampling) captured once in a
     # CUDA graph and replayed: SURVEY 8(f) row 2 -- every call of this library is capturable (no allocation in
     # the C ABI, no synchronisation, launches on the capturing stream)

@@ -153,3 +153,19 @@ def test_raft_small_with_library_block_and_upflow8():
     d32 = _epe(got, ref)
     assert d32 <= 0.002, f"RAFT-small, tf32 build: mean EPE delta {d32:.5f} px"
 
+
+def test_mixed_precision_with_fp16_lookup_and_fp16_mask(reference_run):
+    """--mixed_precision (core/raft.py:98-100, :110-114, :127-128: the three networks under fp16 autocast).  The block
+    then returns fp16 (out_dtype); against the reference block
+    under the same autocast the flow moves by less than autocast itself moves it from the fp32 run, and stays within
+    0.01 px of the fp32 reference."""
+    nets, im1, im2, low, up = reference_run
+    _, ref16 = Hn.raft_forward(nets, im1, im2, iters=12, corr_cls=Hn.TorchCorrBlock, mixed_precision=True)
+    autocast_noise = _epe(ref16, up)
+    assert 1e-5 < autocast_noise < 0.01, f"autocast run differs from fp32 by {autocast_noise:.5f} px (is autocast active?)"
+    # (the traced update block hands the mask over in whatever type its last traced op produces; the half-precision
+    # mask path of the upsampling has its own test in test_gpu_upsample.py)
+    _, got = Hn.raft_forward(nets, im1, im2, iters=12, corr_cls=partial(R.CorrBlock, out_dtype=torch.float16),
+                             upsample_fn=R.upsample_flow, mixed_precision=True)
+    assert _epe(got, ref16) <= 0.01 and _epe(got, up) <= 0.01, (_epe(got, ref16), _epe(got, up))
+
