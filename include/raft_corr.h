@@ -28,7 +28,7 @@ extern "C" {
 #define RC_API
 #endif
 
-#define RC_ABI_VERSION 3
+#define RC_ABI_VERSION 4
 #define RC_MAX_LEVELS 6
 
 /* error codes */
@@ -100,6 +100,8 @@ RC_API int64_t rc_build_workspace_bytes(int B, int D, int H, int W, int math);
  *                  them, core/raft.py:102-107)
  *   pyramid      : out, rc_layout of (B, H, W, num_levels, vol_dtype)
  *   workspace    : >= rc_build_workspace_bytes(...) bytes, 256-byte aligned
+ * The tensor-core modes (RC_MATH_BF16 / _F16 / _TF32) need D % 8 == 0 and num_levels <= 4; other sizes
+ * return RC_EINVAL before anything is launched (RC_MATH_F32 takes any D and up to RC_MAX_LEVELS levels).
  */
 RC_API int rc_build_pyramid(const float *fmap1, const float *fmap2, int B, int D, int H, int W,
                      int num_levels, int vol_dtype, int math, void *pyramid,
@@ -172,12 +174,19 @@ RC_API int64_t rc_build_bwd_workspace_bytes(int B, int D, int H, int W, int num_
 
 /*
  * Backward of rc_build_pyramid: transposes of the three avg_pool2d calls and of
- * the matmul of core/corr.py:58-60 (what autograd runs for train.py:175).
- *   grad_pyramid   : fp32 pyramid (RC_VOL_F32 layout), read only
+ * the matmul of core/corr.py:58-60 (what autograd runs for train.py:175).  Both
+ * contractions run on the tensor cores (tcgen05 kind::tf32) over the gradient
+ * pyramid in place; no library call, nothing allocated, capturable.
+ *   grad_pyramid   : fp32 pyramid (RC_VOL_F32 layout), read only, 16-byte aligned
  *   dfmap1, dfmap2 : fp32 [B, D, H, W], overwritten
+ *   math           : RC_MATH_TF32  one tf32 pass (features rounded to nearest, gradients truncated
+ *                                  to tf32): ~5e-4 relative, the setting for bf16 / tf32 volumes
+ *                    RC_MATH_F32   3xTF32 (every operand split into hi + lo in shared memory, three
+ *                                  MMA passes): fp32-grade, what the reference's fp32 SGEMMs give
+ *   workspace      : >= rc_build_bwd_workspace_bytes(...) bytes, 256-byte aligned
  */
 RC_API int rc_build_bwd(const float *grad_pyramid, const float *fmap1, const float *fmap2, int B, int D,
-                 int H, int W, int num_levels, float *dfmap1, float *dfmap2, void *workspace,
+                 int H, int W, int num_levels, int math, float *dfmap1, float *dfmap2, void *workspace,
                  size_t workspace_bytes, rc_stream_t stream);
 
 /*

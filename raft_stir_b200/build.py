@@ -69,7 +69,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if force or jobs or _stale(LIB, objs):
         cuda_lib = os.path.join(os.path.dirname(os.path.dirname(nvcc)), "lib64")
         cmd = [nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB] + objs + [
-            "-L" + cuda_lib, "-lcublas", "-Xlinker", "-rpath=" + cuda_lib]
+            "-L" + cuda_lib, "-Xlinker", "-rpath=" + cuda_lib]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")

@@ -244,8 +244,10 @@ class CorrBlock:
         ws_bytes = int(L.rc_build_bwd_workspace_bytes(self.B, self.D, self.H, self.W, self.num_levels))
         ws = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=self.device)
         with _guard(self.device):
+            # fp32-math blocks keep fp32-grade gradients (3xTF32); the 16-bit / tf32 builds take the one-pass tf32 backward
+            bwd_math = _lib.RC_MATH_F32 if self.math == _lib.RC_MATH_F32 else _lib.RC_MATH_TF32
             check(L.rc_build_bwd(self._grad_buf.data_ptr(), f1.data_ptr(), f2.data_ptr(), self.B, self.D,
-                                 self.H, self.W, self.num_levels, d1.data_ptr(), d2.data_ptr(),
+                                 self.H, self.W, self.num_levels, bwd_math, d1.data_ptr(), d2.data_ptr(),
                                  ws.data_ptr(), ws_bytes, _stream(f1)), "rc_build_bwd")
         ws.record_stream(torch.cuda.current_stream(self.device))
         self._grad_buf.record_stream(torch.cuda.current_stream(self.device))

@@ -44,8 +44,8 @@ int launch_upflow8_bwd(const float *gout, int B, int C, int H, int W, float *dfl
 // build_bwd.cu
 int64_t build_bwd_workspace_bytes(int B, int D, int H, int W, int num_levels);
 int launch_build_bwd(const float *grad_pyramid, const float *fmap1, const float *fmap2, int B, int D,
-                     int H, int W, const rc_layout &glay, float *dfmap1, float *dfmap2, void *workspace,
-                     size_t workspace_bytes, cudaStream_t s);
+                     int H, int W, const rc_layout &glay, int precise, float *dfmap1, float *dfmap2,
+                     void *workspace, cudaStream_t s);
 
 // Scratch of rc_build_pyramid_static: the packed bf16 operands of the tensor-core
 // build.  In host code this name is only a handle for cudaGetSymbolAddress; the
@@ -100,6 +100,15 @@ static int make_layout(int B, int H, int W, int num_levels, int vol_dtype, rc_la
   return RC_OK;
 }
 
+// Limits of the tensor-core build (build_tc.cu), checked BEFORE anything is launched: the pack kernel writes
+// channel pairs and the fused pyramid epilogue holds four levels.
+static int check_tc_limits(const char *who, int D, int num_levels) {
+  RC_REQUIRE(D % 8 == 0, "%s: the tensor-core build needs D %% 8 == 0 (got %d); use RC_MATH_F32", who, D);
+  RC_REQUIRE(num_levels <= 4, "%s: the tensor-core build supports at most 4 pyramid levels (got %d); use RC_MATH_F32",
+             who, num_levels);
+  return RC_OK;
+}
+
 static int64_t packed_rows2(int H, int W) {
   return (int64_t)ceil_div(W, TB_W) * ceil_div(H, TB_H) * TB_N;
 }
@@ -138,6 +147,8 @@ int rc_build_pyramid(const float *fmap1, const float *fmap2, int B, int D, int H
   if (r) return r;
   cudaStream_t s = (cudaStream_t)stream;
   if (math == RC_MATH_F32) return launch_build_simt(fmap1, fmap2, B, D, H, W, lay, vol_dtype, pyramid, s);
+  r = check_tc_limits("rc_build_pyramid", D, num_levels);
+  if (r) return r;
   const int64_t need = rc_build_workspace_bytes(B, D, H, W, math);
   if (workspace == nullptr || (int64_t)workspace_bytes < need) {
     set_error("rc_build_pyramid: workspace of %zu bytes, need %lld", workspace_bytes, (long long)need);
@@ -159,6 +170,8 @@ int rc_build_pyramid_static(const float *fmap1, const float *fmap2, int B, int D
   RC_REQUIRE(D >= 1, "rc_build_pyramid_static: D=%d", D);
   rc_layout lay;
   int r = make_layout(B, H, W, num_levels, vol_dtype, &lay);
+  if (r) return r;
+  r = check_tc_limits("rc_build_pyramid_static", D, num_levels);
   if (r) return r;
   const int64_t need = rc_build_workspace_bytes(B, D, H, W, RC_MATH_BF16);
   if (need < 0 || need > (int64_t)RC_STATIC_SCRATCH_BYTES) {
@@ -220,9 +233,11 @@ int64_t rc_build_bwd_workspace_bytes(int B, int D, int H, int W, int num_levels)
 }
 
 int rc_build_bwd(const float *grad_pyramid, const float *fmap1, const float *fmap2, int B, int D, int H,
-                 int W, int num_levels, float *dfmap1, float *dfmap2, void *workspace,
+                 int W, int num_levels, int math, float *dfmap1, float *dfmap2, void *workspace,
                  size_t workspace_bytes, rc_stream_t stream) {
   RC_REQUIRE(grad_pyramid && fmap1 && fmap2 && dfmap1 && dfmap2, "rc_build_bwd: NULL pointer");
+  RC_REQUIRE(B >= 1 && D >= 1, "rc_build_bwd: bad sizes B=%d D=%d", B, D);
+  RC_REQUIRE(math == RC_MATH_F32 || math == RC_MATH_TF32, "rc_build_bwd: math %d (RC_MATH_F32 = 3xTF32 or RC_MATH_TF32)", math);
   rc_layout glay;
   int r = make_layout(B, H, W, num_levels, RC_VOL_F32, &glay);
   if (r) return r;
@@ -231,8 +246,8 @@ int rc_build_bwd(const float *grad_pyramid, const float *fmap1, const float *fma
     set_error("rc_build_bwd: workspace of %zu bytes, need %lld", workspace_bytes, (long long)need);
     return RC_ESIZE;
   }
-  return launch_build_bwd(grad_pyramid, fmap1, fmap2, B, D, H, W, glay, dfmap1, dfmap2, workspace,
-                          workspace_bytes, (cudaStream_t)stream);
+  return launch_build_bwd(grad_pyramid, fmap1, fmap2, B, D, H, W, glay, math == RC_MATH_F32, dfmap1, dfmap2,
+                          workspace, (cudaStream_t)stream);
 }
 
 int rc_alt_fwd(const float *fmap1, const float *fmap2, const float *coords, int B, int H1, int W1, int H2,

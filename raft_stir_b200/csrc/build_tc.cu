@@ -630,6 +630,12 @@ int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, con
 
 }  // namespace
 
+// shared with build_bwd.cu (declared in tc_ptx.cuh)
+int encode_tiled(CUtensorMap *map, CUtensorMapDataType dt, int rank, const void *base, const cuuint64_t *dims,
+                 const cuuint64_t *strides_bytes, const cuuint32_t *box, CUtensorMapSwizzle sw, const char *what) {
+  return encode(map, dt, rank, base, dims, strides_bytes, box, sw, what);
+}
+
 int launch_build_tc(const void *f1p, const void *f2p, int B, int D, int H, int W, const rc_layout &lay,
                     int vol_dtype, int math, void *pyramid, cudaStream_t s) {
   if (math == RC_MATH_TF32)

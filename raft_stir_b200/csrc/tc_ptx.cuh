@@ -6,6 +6,9 @@
 #include <stdint.h>
 
 namespace rc {
+// host: cuTensorMapEncodeTiled through the runtime's driver entry point (build_tc.cu); sets the error string on failure
+int encode_tiled(CUtensorMap *map, CUtensorMapDataType dt, int rank, const void *base, const cuuint64_t *dims,
+                 const cuuint64_t *strides_bytes, const cuuint32_t *box, CUtensorMapSwizzle sw, const char *what);
 namespace tc {
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -72,6 +75,15 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *map
       "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
       " [%0], [%1, {%3, %4, %5}], [%2], %6;"
       ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "l"(policy)
+      : "memory");
+}
+// the same without a cache hint (streamed operands)
+__device__ __forceinline__ void tma_load_3d_plain(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1,
+                                                  int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5}], [%2];"
+      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
       : "memory");
 }
 __device__ __forceinline__ void stg16_hint(void *dst, const uint4 &v, uint64_t policy) {
@@ -141,6 +153,14 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 constexpr uint32_t DESC_HI = (1024u >> 4) | (1u << 14) | (2u << 29);
 __device__ __forceinline__ uint32_t desc_lo(uint32_t saddr) { return ((saddr >> 4) & 0x3fffu) | (1u << 16); }
 __device__ __forceinline__ uint64_t desc_make(uint32_t lo) { return ((uint64_t)DESC_HI << 32) | lo; }
+// MN-major operand tile of 32-bit elements (kind::tf32 accepts only this swizzle for MN-major operands): rows of
+// 128 contiguous bytes along M/N, one row per K index, 128 bytes apart; 32-byte chunks XOR-swizzled with the row
+// index mod 4 (TMA: CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B; descriptor layout type 1).  SBO = 512 bytes between groups
+// of 4 K rows, LBO = distance between successive 128-byte spans along M/N.
+constexpr uint32_t DESC_HI_MN32 = (512u >> 4) | (1u << 14) | (1u << 29);
+__device__ __forceinline__ uint64_t desc_make_mn32(uint32_t saddr, uint32_t lbo_bytes) {
+  return ((uint64_t)DESC_HI_MN32 << 32) | ((saddr >> 4) & 0x3fffu) | (((lbo_bytes >> 4) & 0x3fffu) << 16);
+}
 // kind::f16 instruction descriptor: D = F32 (bit 4), A = B = BF16 (bits 7, 10), both K-major, N>>3 at 17, M>>4 at 24
 constexpr uint32_t idesc_bf16(int M, int N) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);

@@ -62,6 +62,21 @@ def test_workspace_sizes():
     assert L.rc_build_bwd_workspace_bytes(1, 256, 55, 128, 4) > 0
 
 
+def test_tensor_core_build_rejects_unsupported_sizes_before_launching():
+    """D % 8 != 0 or more than 4 levels with a tensor-core math mode: RC_EINVAL from the argument checks, i.e. before
+    the pack kernel could be queued (no CUDA call has happened: this runs without a GPU; the pointers are never
+    dereferenced)."""
+    L = _lib.lib()
+    fake = 0x1000   # non-null, 256-byte aligned
+    for D, levels in ((3, 4), (12, 2), (64, 5)):
+        for math in (_lib.RC_MATH_BF16, _lib.RC_MATH_F16, _lib.RC_MATH_TF32):
+            r = L.rc_build_pyramid(fake, fake, 1, D, 64, 64, levels, _lib.RC_VOL_BF16, math, fake, fake, 1 << 40, None)
+            assert r == -1, (D, levels, math, r)
+            assert b"tensor-core build" in L.rc_last_error()
+        r = L.rc_build_pyramid_static(fake, fake, 1, D, 64, 64, levels, _lib.RC_VOL_BF16, fake, None)
+        assert r == -1 and b"tensor-core build" in L.rc_last_error()
+
+
 def test_no_cpu_fallback():
     import raft_stir_b200 as R
     with pytest.raises(RuntimeError, match="CUDA"):
