@@ -133,37 +133,60 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
-def cpu_reference_pairs_per_s(budget_s, max_pairs):
-    """The reference's CPU path (same torch library calls, oracle/torch_port.py)
-    timed on the host cores over a bounded sample of the workload."""
+def cpu_hot_path():
+    """The reference's CPU implementation of the path as a callable (f1, f2, coords_list) -> outputs.
+    kind "reference": the reference's own core/corr.py + core/utils/utils.py, unmodified, staged under
+    oracle/_ref/refcore/ by oracle/stage_ref_python.py (the checkout itself is absent on the GPU box).
+    kind "port": oracle/torch_port.py (the same torch calls) when those files were not staged."""
+    ref_dir = os.path.join(ROOT, "oracle", "_ref", "refcore")
+    if os.path.exists(os.path.join(ref_dir, "corr.py")):
+        if ref_dir not in sys.path:
+            sys.path.insert(0, ref_dir)
+        import warnings
+        warnings.filterwarnings("ignore")          # torch.meshgrid indexing warning of the 2020 code
+        from corr import CorrBlock as RefCorrBlock   # the reference, unmodified
+
+        def run(f1, f2, coords):
+            blk = RefCorrBlock(f1, f2, num_levels=LEVELS, radius=RADIUS)
+            return [blk(c) for c in coords]
+        return run, "reference", "reference core/corr.py CorrBlock (unmodified, oracle/_ref/refcore) on the host CPU"
     from oracle import torch_port as P
+
+    def run(f1, f2, coords):
+        return P.hot_path(f1, f2, coords, RADIUS, LEVELS)
+    return run, "port", "the reference's torch CPU calls via oracle/torch_port.py"
+
+
+def cpu_reference_pairs_per_s(budget_s, max_pairs):
+    """The reference's CPU path timed on the host cores over a bounded sample of the workload."""
+    run, kind, what = cpu_hot_path()
     torch.set_num_threads(os.cpu_count() or 1)
     f1, f2, coords = make_inputs(1, None, seed=0)
     with torch.no_grad():
-        P.hot_path(f1, f2, coords[:1], RADIUS, LEVELS)            # warm-up (thread pools, allocator)
+        run(f1, f2, coords[:1])            # warm-up (thread pools, allocator)
         times = []
         t_start = time.perf_counter()
         while len(times) < max_pairs and (len(times) < 2 or time.perf_counter() - t_start < budget_s):
             t0 = time.perf_counter()
-            P.hot_path(f1, f2, coords, RADIUS, LEVELS)
+            run(f1, f2, coords)
             times.append(time.perf_counter() - t0)
-    return len(times) / sum(times), len(times), torch.get_num_threads()
+    return len(times) / sum(times), len(times), torch.get_num_threads(), kind, what
 
 
 def run_reference(args, rank, world):
+    """--impl reference: the reference's own CPU implementation of the path on all host cores.  One step = ONE
+    frame pair (build + 12 lookups): a bounded sample of the GPU arm's 64-pair step; both arms report pairs/s."""
     if rank != 0:
         return
-    per_step = 1
-    _ = per_step
-    from oracle import torch_port as P
+    run, kind, what = cpu_hot_path()
     torch.set_num_threads(os.cpu_count() or 1)
     f1, f2, coords = make_inputs(1, None, seed=0)
     with torch.no_grad():
         for _ in range(max(args.warmup, 1)):
-            P.hot_path(f1, f2, coords, RADIUS, LEVELS)
+            run(f1, f2, coords)
         t0 = time.perf_counter()
         for _ in range(args.steps):
-            P.hot_path(f1, f2, coords, RADIUS, LEVELS)
+            run(f1, f2, coords)
         dt = time.perf_counter() - t0
     v = args.steps / dt
     cores = torch.get_num_threads()
@@ -172,9 +195,10 @@ def run_reference(args, rank, world):
         "unit": "pairs/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": max(args.warmup, 1),
         "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "pairs_per_step": 1, "device": "host CPU"},
-        "cpu_baseline": {"value": v, "unit": "pairs/s", "cores": cores, "kind": "port",
-                         "sample": "1 pair per step (build + 12 lookups), reference's torch CPU calls via oracle/torch_port.py"},
+        "config": {"workload": WORKLOAD, "pairs_per_step": 1, "device": "host CPU",
+                   "note": "per-pair throughput of the same workload; the GPU arm runs 64 pairs per step"},
+        "cpu_baseline": {"value": v, "unit": "pairs/s", "cores": cores, "kind": kind,
+                         "sample": f"1 pair per step (build + 12 lookups), {what}"},
         "e2e": {"value": v, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
@@ -358,9 +382,9 @@ def main():
     cpu = None
     extras = {}
     if rank == 0 and world == 1:
-        v, npairs, cores = cpu_reference_pairs_per_s(args.cpu_budget, max_pairs=40)
-        cpu = {"value": v, "unit": "pairs/s", "cores": cores, "kind": "port",
-               "sample": f"{npairs} pairs of {WORKLOAD} via oracle/torch_port.py (the reference's torch CPU calls)"}
+        v, npairs, cores, kind, what = cpu_reference_pairs_per_s(args.cpu_budget, max_pairs=40)
+        cpu = {"value": v, "unit": "pairs/s", "cores": cores, "kind": kind,
+               "sample": f"{npairs} pairs of {WORKLOAD}: {what}"}
         if not args.no_extras:
             extras = run_extras(R, device, args, pk)
 

@@ -262,12 +262,18 @@ class AlternateCorrBlock:
     Like the reference, the output carries no autograd history."""
 
     def __init__(self, fmap1, fmap2, num_levels: int = 4, radius: int = 4, *, math: Optional[str] = None):
-        """math: "fp32" (default; CUDA-core FMA, the reference kernel's arithmetic), "bf16" or "fp16" (the block's
-        local volume on the tensor cores, 16-bit operands, fp32 accumulate; needs D % 64 == 0; fp16 keeps three more
-        mantissa bits of the features and saturates beyond +-65 504).  RAFT_ALT_MATH sets the default."""
+        """math: "bf16" (the default when D % 64 == 0, which RAFT-basic's 256 and RAFT-small's 128 channels are: the
+        block's local volume on the tensor cores, 16-bit operands, fp32 accumulate -- the precision the north star
+        names, and 20-30x faster than the CUDA-core path), "fp16" (the same with three more mantissa bits of the
+        features; saturates beyond +-65 504) or "fp32" (CUDA-core FMA, the reference kernel's arithmetic; the default
+        for other channel counts and the opt-in for 1e-4 parity).  RAFT_ALT_MATH sets the default."""
         self.num_levels = num_levels
         self.radius = radius
-        math = math or os.environ.get("RAFT_ALT_MATH", "fp32")
+        if math is None:
+            math = os.environ.get("RAFT_ALT_MATH")
+        if math is None:
+            D_ = int(fmap1.shape[1]) if isinstance(fmap1, torch.Tensor) and fmap1.dim() == 4 else 0
+            math = "bf16" if D_ >= 64 and D_ % 64 == 0 else "fp32"
         if math not in ("fp32", "bf16", "fp16"):
             raise RaftCorrError(f"math={math!r}: expected fp32|bf16|fp16")
         self.math = math

@@ -74,6 +74,7 @@ struct BwdParams {
   int items_per_pair;       // (qt + sum t2) * n_dt
   long long total_items;
   int Kq;                   // dpool row pitch
+  int seg;                  // k-blocks accumulated in TMEM before the epilogue takes the partial sum
   uint32_t idesc1, idesc2;
   float *dfmap1;            // [B][D][N]
   float *dpool;             // [B][D][Kq]
@@ -195,35 +196,40 @@ build_bwd_tc_kernel(const __grid_constant__ BwdMaps maps, const BwdParams p) {
       uint32_t st = 0, ph = 0, i = 0, lph = 0;
       for (long long idx = blockIdx.x; idx < p.total_items; idx += gridDim.x) {
         const Item it = decode_item(p, idx);
-        const uint32_t acc = i & 1;
-        mbar_wait(bar_t_empty + 8 * acc, ((i >> 1) & 1) ^ 1);
-        ++i;
-        fence_after();
-        const uint32_t d_tmem = tmem_base + acc * MAXDT;
         const bool mn = it.kind == 2;
         const uint32_t idesc = mn ? p.idesc2 : p.idesc1;
-        for (int kb = 0; kb < it.nkb; ++kb) {
-          mbar_wait(bar_full + 8 * st, ph);
-          if (PRECISE) { mbar_wait(bar_lo_full, lph); }
+        for (int kb0 = 0; kb0 < it.nkb; kb0 += p.seg) {
+          // one segment of the contraction per accumulator: the tensor core's fp32 accumulator truncates on every
+          // add, an error that grows with the number of adds; partial sums are combined by the epilogue in fp32
+          const uint32_t acc = i & 1;
+          mbar_wait(bar_t_empty + 8 * acc, ((i >> 1) & 1) ^ 1);
+          ++i;
           fence_after();
-          const uint32_t a_addr = sRing + st * SLOT, b_addr = a_addr + A_BYTES;
+          const uint32_t d_tmem = tmem_base + acc * MAXDT;
+          const int kend = min(it.nkb, kb0 + p.seg);
+          for (int kb = kb0; kb < kend; ++kb) {
+            mbar_wait(bar_full + 8 * st, ph);
+            if (PRECISE) { mbar_wait(bar_lo_full, lph); }
+            fence_after();
+            const uint32_t a_addr = sRing + st * SLOT, b_addr = a_addr + A_BYTES;
 #pragma unroll
-          for (int pass = 0; pass < (PRECISE ? 3 : 1); ++pass) {
-            // pass 0: hi * hi   pass 1: lo * hi   pass 2: hi * lo
-            const uint32_t aa = pass == 1 ? sLo : a_addr;
-            const uint32_t bb = pass == 2 ? sLo + A_BYTES : b_addr;
+            for (int pass = 0; pass < (PRECISE ? 3 : 1); ++pass) {
+              // pass 0: hi * hi   pass 1: lo * hi   pass 2: hi * lo
+              const uint32_t aa = pass == 1 ? sLo : a_addr;
+              const uint32_t bb = pass == 2 ? sLo + A_BYTES : b_addr;
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              const uint64_t adesc = mn ? desc_make_mn32(aa + k * 1024, 4096) : desc_make(desc_lo(aa + k * 32));
-              const uint64_t bdesc = desc_make(desc_lo(bb + k * 32));
-              umma_tf32(d_tmem, adesc, bdesc, idesc, (kb | k | pass) != 0);
+              for (int k = 0; k < 4; ++k) {
+                const uint64_t adesc = mn ? desc_make_mn32(aa + k * 1024, 4096) : desc_make(desc_lo(aa + k * 32));
+                const uint64_t bdesc = desc_make(desc_lo(bb + k * 32));
+                umma_tf32(d_tmem, adesc, bdesc, idesc, ((kb - kb0) | k | pass) != 0);
+              }
             }
+            umma_commit(bar_empty + 8 * st);         // raw stage free once these MMAs retire
+            if (PRECISE) { umma_commit(bar_lo_empty); lph ^= 1; }
+            if (++st == STAGES) { st = 0; ph ^= 1; }
           }
-          umma_commit(bar_empty + 8 * st);         // raw stage free once these MMAs retire
-          if (PRECISE) { umma_commit(bar_lo_empty); lph ^= 1; }
-          if (++st == STAGES) { st = 0; ph ^= 1; }
+          umma_commit(bar_t_full + 8 * acc);
         }
-        umma_commit(bar_t_full + 8 * acc);
       }
     }
   } else if (warp < CONV_WARP0) {
@@ -232,8 +238,6 @@ build_bwd_tc_kernel(const __grid_constant__ BwdMaps maps, const BwdParams p) {
     uint32_t i = 0;
     for (long long idx = blockIdx.x; idx < p.total_items; idx += gridDim.x) {
       const Item it = decode_item(p, idx);
-      const uint32_t acc = i & 1, t_par = (i >> 1) & 1;
-      ++i;
       const int row = it.mt * BM + quarter * 32 + lane;
       float *out;
       long long pitch;
@@ -248,22 +252,34 @@ build_bwd_tc_kernel(const __grid_constant__ BwdMaps maps, const BwdParams p) {
         ok = true;                                 // every level's span on the k axis is padded to whole items
       }
       const int d0 = it.dt * p.DT;
-      mbar_wait(bar_t_full + 8 * acc, t_par);
-      fence_after();
-      const uint32_t taddr = tmem_base + acc * MAXDT + ((uint32_t)(quarter * 32) << 16);
-      for (int c = 0; c < p.DT; c += 16) {
-        uint32_t v[16];
-        tmem_ld16(taddr + c, v);
-        tmem_ld_wait();
+      for (int kb0 = 0; kb0 < it.nkb; kb0 += p.seg) {
+        const uint32_t acc = i & 1, t_par = (i >> 1) & 1;
+        ++i;
+        mbar_wait(bar_t_full + 8 * acc, t_par);
+        fence_after();
+        const uint32_t taddr = tmem_base + acc * MAXDT + ((uint32_t)(quarter * 32) << 16);
+        for (int c = 0; c < p.DT; c += 16) {
+          uint32_t v[16];
+          tmem_ld16(taddr + c, v);
+          tmem_ld_wait();
+          if (kb0 == 0) {
 #pragma unroll
-        for (int r = 0; r < 16; ++r) {
-          const int d = d0 + c + r;
-          if (ok && d < p.D) out[(long long)d * pitch] = __uint_as_float(v[r]);
+            for (int r = 0; r < 16; ++r) {
+              const int d = d0 + c + r;
+              if (ok && d < p.D) out[(long long)d * pitch] = __uint_as_float(v[r]);
+            }
+          } else {          // later segments: this thread wrote the same addresses before
+#pragma unroll
+            for (int r = 0; r < 16; ++r) {
+              const int d = d0 + c + r;
+              if (ok && d < p.D) out[(long long)d * pitch] += __uint_as_float(v[r]);
+            }
+          }
         }
+        fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_t_empty + 8 * acc);
       }
-      fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bar_t_empty + 8 * acc);
     }
   } else if (PRECISE) {
     // ===================================================== splitters: lo = value - (upper 19 bits of value)
@@ -306,9 +322,10 @@ build_bwd_tc_kernel(const __grid_constant__ BwdMaps maps, const BwdParams p) {
 // ---------------------------------------------------------------- operands of the two GEMMs
 struct PrepLevels {
   int L, H, W;
-  int Hl[ML], Wl[ML], tiles_x[ML];
-  int koffp[ML];
-  long long slab[ML];
+  int Hl[ML], Wl[ML], tiles_y[ML], tiles_x[ML];
+  int koffp[ML], kseg[ML];       // level l's span on f2pad's k axis: offset, length (slab rounded up to 32)
+  int soff[ML];                  // offset of level l's logical map in shared memory (levels >= 1)
+  int koffq[ML];                 // level l's offset on dpool's k axis
 };
 
 __device__ __forceinline__ float round_tf32(float v) {
@@ -317,68 +334,97 @@ __device__ __forceinline__ float round_tf32(float v) {
   return __uint_as_float(r);
 }
 
-// blockIdx.x = b * Dp + d;  blockIdx.y = chunk of 256 along [0, Npad) then [0, Kp)
-//   f1r  [b][d][q]                       = s * fmap1[b][d][q]                                    (0 for d >= D, q >= N)
-//   f2pad[b][d][koffp_l + tile_offset]   = s * mean of the 2^l x 2^l block of fmap2[b][d]        (0 in the padding)
+// One block per (pair, channel) row: blockIdx.x = b * Dp + d.
+//   f1r  [b][d][q]                       = s * fmap1[b][d][q]                               (0 for d >= D, q >= N)
+//   f2pad[b][d][koffp_l + tile_offset]   = s * level l of the 2x2 mean pyramid of fmap2[b][d] (0 in the padding)
+// Levels >= 1 are pooled level by level in shared memory (the floor-truncating avg_pool2d chain of
+// core/corr.py:24-27); every level is then written in slab order, one row of 4 x 4 tiles at a time, so that
+// stores are contiguous and no index needs a division by a tile count.
 template <bool ROUND>
 __global__ void __launch_bounds__(256)
 bwd_prep_kernel(const float *__restrict__ fmap1, const float *__restrict__ fmap2, float *__restrict__ f1r,
-                float *__restrict__ f2pad, int D, int Dp, int N, int Npad, int Kp, int chunks1, float s,
-                PrepLevels f) {
-  const int bd = blockIdx.x;
+                float *__restrict__ f2pad, int D, int Dp, int N, int Npad, int Kp, float s, PrepLevels f) {
+  extern __shared__ float pooled[];             // logical maps of levels 1 .. L-1
+  const int bd = blockIdx.x, tid = threadIdx.x;
   const int b = bd / Dp, d = bd - b * Dp;
-  const bool live = d < D;
-  if ((int)blockIdx.y < chunks1) {
-    const int q = blockIdx.y * 256 + threadIdx.x;
-    if (q >= Npad) return;
-    float v = 0.f;
-    if (live && q < N) v = s * __ldg(fmap1 + ((size_t)b * D + d) * N + q);
-    f1r[(size_t)bd * Npad + q] = ROUND ? round_tf32(v) : v;
+  float *o1 = f1r + (size_t)bd * Npad;
+  float *o2 = f2pad + (size_t)bd * Kp;
+  if (d >= D) {                                 // channel padding up to a multiple of 16: zero rows
+    for (int i = tid; i < Npad; i += 256) o1[i] = 0.f;
+    for (int i = tid; i < Kp; i += 256) o2[i] = 0.f;
     return;
   }
-  const int kk = (blockIdx.y - chunks1) * 256 + threadIdx.x;
-  if (kk >= Kp) return;
-  float v = 0.f;
-  if (live) {
-    int l = 0;
-    while (l < f.L - 1 && kk >= f.koffp[l + 1]) ++l;
-    const int r = kk - f.koffp[l];
-    if (r < f.slab[l]) {
-      const int tile = r >> 4, in = r & 15;
-      const int ty = tile / f.tiles_x[l], tx = tile - ty * f.tiles_x[l];
-      const int y = ty * TILE_H + (in >> 2), x = tx * 4 + (in & 3);
-      if (y < f.Hl[l] && x < f.Wl[l]) {
-        const int k = 1 << l;
-        const float *src = fmap2 + ((size_t)b * D + d) * N + (size_t)(y * k) * f.W + x * k;
-        float a = 0.f;
-        for (int dy = 0; dy < k; ++dy)
-          for (int dx = 0; dx < k; ++dx) a += __ldg(src + (size_t)dy * f.W + dx);
-        v = s * a / (float)(k * k);
+  const float *in1 = fmap1 + ((size_t)b * D + d) * N;
+  const float *in2 = fmap2 + ((size_t)b * D + d) * N;
+  for (int q = tid; q < Npad; q += 256) {
+    const float v = q < N ? s * __ldg(in1 + q) : 0.f;
+    o1[q] = ROUND ? round_tf32(v) : v;
+  }
+  // pooled levels, logical layout, unscaled
+  for (int l = 1; l < f.L; ++l) {
+    const int Wl = f.Wl[l], n = f.Hl[l] * Wl;
+    float *dst = pooled + f.soff[l];
+    if (l == 1) {
+      for (int i = tid; i < n; i += 256) {
+        const int y = i / Wl, x = i - y * Wl;
+        const float *p0 = in2 + (size_t)(2 * y) * f.W + 2 * x;
+        dst[i] = 0.25f * ((__ldg(p0) + __ldg(p0 + 1)) + (__ldg(p0 + f.W) + __ldg(p0 + f.W + 1)));
+      }
+    } else {
+      const float *src = pooled + f.soff[l - 1];
+      const int Ws = f.Wl[l - 1];
+      for (int i = tid; i < n; i += 256) {
+        const int y = i / Wl, x = i - y * Wl;
+        const float *p0 = src + (2 * y) * Ws + 2 * x;
+        dst[i] = 0.25f * ((p0[0] + p0[1]) + (p0[Ws] + p0[Ws + 1]));
       }
     }
+    __syncthreads();
   }
-  f2pad[(size_t)bd * Kp + kk] = ROUND ? round_tf32(v) : v;
+  // slab order
+  for (int l = 0; l < f.L; ++l) {
+    const int Hl = f.Hl[l], Wl = f.Wl[l];
+    const int row_elems = f.tiles_x[l] * 16;            // one row of tiles, contiguous in the slab
+    const float *src = l == 0 ? nullptr : pooled + f.soff[l];
+    float *dst = o2 + f.koffp[l];
+    for (int ty = 0; ty < f.tiles_y[l]; ++ty) {
+      for (int i = tid; i < row_elems; i += 256) {
+        const int y = ty * TILE_H + ((i >> 2) & 3), x = (i >> 4) * 4 + (i & 3);
+        float v = 0.f;
+        if (y < Hl && x < Wl) v = s * (l == 0 ? __ldg(in2 + (size_t)y * f.W + x) : src[y * Wl + x]);
+        dst[ty * row_elems + i] = ROUND ? round_tf32(v) : v;
+      }
+    }
+    for (int i = f.tiles_y[l] * row_elems + tid; i < f.kseg[l]; i += 256) dst[i] = 0.f;
+  }
 }
 
-struct FoldLevels {
-  int L;
-  int Hl[ML], Wl[ML], tiles_x[ML];
-  int koffq[ML];
-};
-
-// blockIdx.x = b * D + d;  blockIdx.y = chunk of 256 pixels
+// One block per (pair, channel) row of dfmap2: blockIdx.x = b * D + d.
+//   dfmap2[b][d][y][x] = sum_l dpool_l[b][d][y >> l][x >> l] / 4^l   (inside level l's footprint)
+// The dpool spans of levels >= 1 (a quarter of the row at most) are staged in shared memory in slab order; level 0
+// is read in place, 16 bytes of a tile row at a time.
 __global__ void __launch_bounds__(256)
-bwd_fold_kernel(const float *__restrict__ dpool, float *__restrict__ dfmap2, int N, int W, int Kq, FoldLevels f) {
-  const int r = blockIdx.y * 256 + threadIdx.x;
-  if (r >= N) return;
+bwd_fold_kernel(const float *__restrict__ dpool, float *__restrict__ dfmap2, int N, int Kq, int stage_elems,
+                PrepLevels f) {
+  extern __shared__ float coarse[];             // dpool[koffq_1 ...), slab order
+  const int tid = threadIdx.x;
   const float *row = dpool + (size_t)blockIdx.x * Kq;
-  const int y = r / W, x = r - y * W;
-  float v = 0.f, w = 1.f;
-  for (int l = 0; l < f.L; ++l, w *= 0.25f) {
-    const int yl = y >> l, xl = x >> l;
-    if (yl < f.Hl[l] && xl < f.Wl[l]) v += w * __ldg(row + f.koffq[l] + tile_offset<float>(yl, xl, f.tiles_x[l]));
+  const int base1 = f.L > 1 ? f.koffq[1] : 0;
+  for (int i = tid; i < stage_elems; i += 256) coarse[i] = __ldg(row + base1 + i);
+  __syncthreads();
+  float *out = dfmap2 + (size_t)blockIdx.x * N;
+  const int W = f.W;
+  for (int r = tid; r < N; r += 256) {
+    const int y = r / W, x = r - y * W;
+    float v = __ldg(row + tile_offset<float>(y, x, f.tiles_x[0]));
+    float w = 0.25f;
+    for (int l = 1; l < f.L; ++l, w *= 0.25f) {
+      const int yl = y >> l, xl = x >> l;
+      if (yl < f.Hl[l] && xl < f.Wl[l])
+        v += w * coarse[f.koffq[l] - base1 + (int)tile_offset<float>(yl, xl, f.tiles_x[l])];
+    }
+    out[r] = v;
   }
-  dfmap2[(size_t)blockIdx.x * N + r] = v;
 }
 
 struct Geometry {
@@ -428,20 +474,28 @@ int launch_build_bwd(const float *gpyr, const float *fmap1, const float *fmap2, 
   float *dpool = (float *)((char *)workspace + q.f1r_bytes + q.f2pad_bytes);
   const float scale = 1.0f / sqrtf((float)D);
 
+  PrepLevels f{};
+  f.L = L; f.H = H; f.W = W;
+  int pooled_elems = 0;
+  for (int l = 0; l < L; ++l) {
+    f.Hl[l] = g.H[l]; f.Wl[l] = g.W[l]; f.tiles_y[l] = g.tiles_y[l]; f.tiles_x[l] = g.tiles_x[l];
+    f.koffp[l] = q.koffp[l];
+    f.kseg[l] = (int)round_up64(g.slab[l], KBE);
+    f.koffq[l] = q.koffq[l];
+    f.soff[l] = pooled_elems;
+    if (l >= 1) pooled_elems += g.H[l] * g.W[l];
+  }
+  int max_optin = 0, dev = 0;
+  RC_CUDA(cudaGetDevice(&dev));
+  RC_CUDA(cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+
   // ---- 1. operands
   {
-    PrepLevels f{};
-    f.L = L; f.H = H; f.W = W;
-    for (int l = 0; l < L; ++l) {
-      f.Hl[l] = g.H[l]; f.Wl[l] = g.W[l]; f.tiles_x[l] = g.tiles_x[l];
-      f.koffp[l] = q.koffp[l]; f.slab[l] = g.slab[l];
-    }
-    const int chunks1 = ceil_div(q.Npad, 256), chunks2 = ceil_div(q.Kp, 256);
-    dim3 grid((unsigned)(B * q.Dp), (unsigned)(chunks1 + chunks2));
-    if (precise)
-      bwd_prep_kernel<false><<<grid, 256, 0, s>>>(fmap1, fmap2, f1r, f2pad, D, q.Dp, N, q.Npad, q.Kp, chunks1, scale, f);
-    else
-      bwd_prep_kernel<true><<<grid, 256, 0, s>>>(fmap1, fmap2, f1r, f2pad, D, q.Dp, N, q.Npad, q.Kp, chunks1, scale, f);
+    const size_t smem = (size_t)pooled_elems * sizeof(float);
+    RC_REQUIRE(smem <= (size_t)max_optin, "rc_build_bwd: feature map %dx%d too large", H, W);
+    auto kern = precise ? bwd_prep_kernel<false> : bwd_prep_kernel<true>;
+    if (smem > 48 * 1024) RC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<(unsigned)(B * q.Dp), 256, smem, s>>>(fmap1, fmap2, f1r, f2pad, D, q.Dp, N, q.Npad, q.Kp, scale, f);
     RC_LAUNCH_CHECK("bwd_prep_kernel");
   }
 
@@ -465,6 +519,7 @@ int launch_build_bwd(const float *gpyr, const float *fmap1, const float *fmap2, 
     p.items_per_pair = items * p.n_dt;
     p.total_items = (long long)B * p.items_per_pair;
     p.Kq = q.Kq;
+    p.seg = precise ? 48 : (1 << 30);
     p.idesc1 = idesc_tf32(BM, q.DT, false);
     p.idesc2 = idesc_tf32(BM, q.DT, true);
     p.dfmap1 = dfmap1;
@@ -495,8 +550,7 @@ int launch_build_bwd(const float *gpyr, const float *fmap1, const float *fmap2, 
       if ((r = encode_tiled(&maps.f1r, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, f1r, dims, str, box,
                             CU_TENSOR_MAP_SWIZZLE_128B, "fmap1"))) return r;
     }
-    int dev = 0, sms = 0;
-    RC_CUDA(cudaGetDevice(&dev));
+    int sms = 0;
     RC_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     const int grid = p.total_items < sms ? (int)p.total_items : sms;
     if (precise) {
@@ -513,14 +567,12 @@ int launch_build_bwd(const float *gpyr, const float *fmap1, const float *fmap2, 
 
   // ---- 3. dfmap2
   {
-    FoldLevels f{};
-    f.L = L;
-    for (int l = 0; l < L; ++l) {
-      f.Hl[l] = g.H[l]; f.Wl[l] = g.W[l]; f.tiles_x[l] = g.tiles_x[l];
-      f.koffq[l] = q.koffq[l];
-    }
-    dim3 grid((unsigned)(B * D), (unsigned)ceil_div(N, 256));
-    bwd_fold_kernel<<<grid, 256, 0, s>>>(dpool, dfmap2, N, W, q.Kq, f);
+    const int stage_elems = L > 1 ? q.Kq - q.koffq[1] : 0;
+    const size_t smem = (size_t)stage_elems * sizeof(float);
+    RC_REQUIRE(smem <= (size_t)max_optin, "rc_build_bwd: feature map %dx%d too large", H, W);
+    if (smem > 48 * 1024)
+      RC_CUDA(cudaFuncSetAttribute(bwd_fold_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    bwd_fold_kernel<<<(unsigned)(B * D), 256, smem, s>>>(dpool, dfmap2, N, q.Kq, stage_elems, f);
     RC_LAUNCH_CHECK("bwd_fold_kernel");
   }
   return RC_OK;

@@ -6,10 +6,11 @@ Tolerances, as |got - ref| <= tol * (|ref| + rms(ref)) for EVERY element, plus a
   math = RC_MATH_TF32 : 2e-3 (rms 5e-4).  One kind::tf32 pass: features rounded to tf32, gradients truncated to tf32
                         by the tensor core; each product carries ~3e-4 of independent relative error, so the worst of
                         10^6..10^7 outputs sits near 5 sigma = 1.5e-3 (measured 1.1e-3..1.5e-3), whatever the rounding.
-  math = RC_MATH_F32  : 2.5e-4 (rms 3e-5).  3xTF32 removes the operand rounding; what is left is the tensor core's
-                        fp32 accumulator, whose adds truncate: the error grows linearly with the contraction length
-                        (measured 7e-6 at 374 queries, 5e-5 at 2 852, 1.2e-4 at 7 040).  The reference's backward is an
-                        fp32 SGEMM (round-to-nearest FMA chain, ~1e-6).
+  math = RC_MATH_F32  : 6e-5 (rms 1.2e-5).  3xTF32 removes the operand rounding; what is left is the tensor core's
+                        fp32 accumulator, whose adds truncate: accumulated in one go the error grows linearly with the
+                        contraction length (measured 7e-6 at 374 queries, 5e-5 at 2 852, 1.2e-4 at 7 040), so the kernel
+                        accumulates 48 k-blocks at a time in TMEM and adds the partial sums in fp32 registers
+                        (measured 2.5e-5 max / 6e-6 rms at every size).  The reference's backward is an fp32 SGEMM.
 """
 import json
 import os
@@ -100,7 +101,7 @@ def test_build_bwd_matches_autograd(shape, math):
     out = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
     if os.path.isdir(out):
         json.dump(RESULTS, open(os.path.join(out, "build_bwd_errors.json"), "w"), indent=1)
-    tol, tol_rms = (2e-3, 5e-4) if math == "tf32" else (2.5e-4, 3e-5)
+    tol, tol_rms = (2e-3, 5e-4) if math == "tf32" else (6e-5, 1.2e-5)
     assert e1 <= tol and s1 <= tol_rms, f"dfmap1 {shape} {math}: max {e1:.3e} (<= {tol:g}), rms {s1:.3e} (<= {tol_rms:g})"
     assert e2 <= tol and s2 <= tol_rms, f"dfmap2 {shape} {math}: max {e2:.3e} (<= {tol:g}), rms {s2:.3e} (<= {tol_rms:g})"
 

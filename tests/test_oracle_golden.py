@@ -152,3 +152,29 @@ def test_upsample_is_a_convex_combination():
     up = U.upsample_flow(flow, rng.normal(0, 2, (1, 576, 4, 5)))
     np.testing.assert_allclose(up[:, :, 8:-8, 8:-8], 12.0, rtol=1e-12)
     assert (np.abs(up) <= 12.0 + 1e-9).all()
+
+
+# ------------------------------------------------------------------ BASELINE shapes (subsampled goldens)
+@pytest.mark.parametrize("name", ["sintel", "chairs"])
+def test_oracle_matches_reference_at_baseline_shapes(name):
+    """oracle/make_golden_shapes.py froze the reference CorrBlock's lookups at 256 random queries of the Sintel and
+    FlyingChairs feature shapes; the numpy oracle, evaluated for those queries only, must reproduce them (1e-4)."""
+    import os
+    from oracle import make_golden_shapes as G
+    gold = dict(np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", f"shape_{name}.npz")))
+    inp = G.make_inputs(name)
+    np.testing.assert_allclose(G.checksums(inp), gold["checksums"], rtol=1e-12, atol=1e-9)
+    H, W, _ = G.SHAPES[name]
+    q = gold["queries"]
+    f1 = inp["f1"].numpy().reshape(G.D, H * W)[:, q].astype(np.float64)      # [D, 256]
+    f2 = inp["f2"].numpy().reshape(G.D, H * W).astype(np.float64)
+    vol = (f1.T @ f2 / np.sqrt(np.float64(G.D))).reshape(len(q), H, W)
+    pyr = [vol]
+    for _ in range(G.LEVELS - 1):
+        pyr.append(O._pool2(pyr[-1]))
+    for l in range(1, G.LEVELS):
+        np.testing.assert_allclose(pyr[l][:16], gold[f"pyr{l}"], rtol=1e-4, atol=2e-5, err_msg=f"{name} level {l}")
+    for kind in ("rand", "int"):
+        c = inp[f"coords_{kind}"].numpy().reshape(1, 2, H * W)[:, :, q].reshape(1, 2, len(q), 1).astype(np.float64)
+        out = O.window_lookup(pyr, c, G.RADIUS)                                # [1, 324, 256, 1]
+        np.testing.assert_allclose(out[0, :, :, 0], gold[f"out_{kind}"], rtol=1e-4, atol=2e-5, err_msg=f"{name} lookup {kind}")
