@@ -59,16 +59,24 @@ def ncu_traffic(kernel, batch, storage):
 
 
 def write_only_gbs(device):
-    """HBM bandwidth of a pure write stream (fill of 1 GiB), measured live: the ceiling of the volume
-    build, which writes 16x more than it reads.  (The copy figure in MEASURED_PEAKS.json is read + write.)"""
-    buf = torch.empty(1 << 29, dtype=torch.bfloat16, device=device)
+    """HBM bandwidth of a pure write stream, measured live with cudaMemsetAsync over 2 GiB (torch's zero_ is that
+    call).  Round 1 quoted torch's fill kernel here (3.9 TB/s) as "the" write-only ceiling; tools/store_probe.cu
+    (profiles/r2b_store_probe.jsonl, hand-written stores) shows that was the fill kernel's limit, not the memory's:
+    memset 7.3 TB/s, bulk shared->global copies 6.4 TB/s, the build's own access pattern (256 contiguous bytes per
+    query row per visit) 5.9 TB/s with plain 16-byte stores."""
+    buf = torch.empty(1 << 31, dtype=torch.uint8, device=device)
     best = 1e9
-    for i in range(6):
+    for i in range(5):
         e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
-        e0.record(); buf.fill_(1.0); e1.record(); torch.cuda.synchronize()
+        e0.record(); buf.zero_(); e1.record(); torch.cuda.synchronize()
         if i:
             best = min(best, e0.elapsed_time(e1))
-    return (1 << 30) / best / 1e6
+    return (1 << 31) / best / 1e6
+
+
+# hand-written store probe (tools/store_probe.cu on this pool's B200, profiles/r2b_store_probe.jsonl): plain 16-byte
+# stores in the build's access pattern, 256 contiguous bytes per query row per visit
+PROBE_CHUNK256_GBS = 5914.5
 
 
 def make_inputs(batch, device, seed):
@@ -212,10 +220,10 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=64,
                     help="frame pairs per GPU per step (BASELINE configs[2]: batch 64 Sintel-shape pairs)")
-    ap.add_argument("--e2e-batch", type=int, default=16, help="frame pairs per end-to-end step (host buffers are pinned)")
+    ap.add_argument("--e2e-batch", type=int, default=0, help="frame pairs per end-to-end step (0 = the same as --batch)")
     ap.add_argument("--storage", default="bf16", choices=["bf16", "fp16", "fp32"])
     ap.add_argument("--math", default="bf16", choices=["bf16", "fp16", "tf32"], help="operand type of the tensor-core build")
-    ap.add_argument("--e2e-steps", type=int, default=5)
+    ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU baseline work")
     ap.add_argument("--no-extras", action="store_true")
     args = ap.parse_args()
@@ -310,73 +318,129 @@ def main():
     look_gbs = look_bytes / (look_avg * 1e-3) / 1e9
     build_gbs = build_bytes / (build_avg * 1e-3) / 1e9
     build_tf = B * BUILD_FLOPS / (build_avg * 1e-3) / 1e12
-    # the per-iteration kernel (12 of the 14 launches of a step, half of its time) is the one the roofline
-    # object describes; the build's numbers, which take the other half, are in `kernels`
-    lookups_dominate = True
+    # `roofline` describes the per-iteration kernel (12 of the 14 launches of a step, half of its time);
+    # `roofline_build` the other half (pack + tcgen05 build, timed together as the API issues them)
     wr_gbs = write_only_gbs(device)
-    if lookups_dominate:
-        roof = {"kernel": "lookup_fwd_kernel", "bound": "hbm", "achieved": look_gbs, "peak": pk["hbm_gbs"], "unit": "GB/s",
-                "frac": look_gbs / pk["hbm_gbs"], "traffic": ncu_traffic("lookup_fwd_kernel", B, args.storage),
-                "peak_source": pk["source"],
-                "algorithmic_bytes_per_launch": look_bytes, "avg_launch_ms": look_avg}
-    else:
-        roof = {"kernel": "build_pyramid_tc_kernel(+pack)", "bound": "hbm", "achieved": build_gbs, "peak": pk["hbm_gbs"],
-                "unit": "GB/s", "frac": build_gbs / pk["hbm_gbs"],
-                "traffic": ncu_traffic("build_pyramid_tc_kernel", B, args.storage), "peak_source": pk["source"],
-                "algorithmic_bytes_per_launch": build_bytes, "avg_launch_ms": build_avg}
+    roof = {"kernel": "lookup_fwd_kernel", "bound": "hbm", "achieved": look_gbs, "peak": pk["hbm_gbs"], "unit": "GB/s",
+            "frac": look_gbs / pk["hbm_gbs"], "traffic": ncu_traffic("lookup_fwd_kernel", B, args.storage),
+            "peak_source": pk["source"],
+            "algorithmic_bytes_per_launch": look_bytes, "avg_launch_ms": look_avg}
+    roof_build = {"kernel": "pack_features_kernel + build_pyramid_tc_kernel", "bound": "hbm", "achieved": build_gbs,
+                  "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": build_gbs / pk["hbm_gbs"],
+                  "traffic": ncu_traffic("build_pyramid_tc_kernel", B, args.storage), "peak_source": pk["source"],
+                  "algorithmic_bytes_per_launch": build_bytes, "avg_launch_ms": build_avg,
+                  "tensor": {"achieved": build_tf, "peak": pk["bf16_tflops_sustained"], "unit": "TFLOP/s",
+                             "frac": build_tf / pk["bf16_tflops_sustained"]},
+                  "write_stream": {"memset_GB/s_live": wr_gbs, "frac_of_memset": build_gbs / wr_gbs,
+                                   "probe_256B_pieces_GB/s": PROBE_CHUNK256_GBS,
+                                   "frac_of_probe": build_gbs / PROBE_CHUNK256_GBS}}
     kernels = {
         "lookup_fwd": {"avg_ms": look_avg, "GB/s": look_gbs, "frac_hbm": look_gbs / pk["hbm_gbs"], "share_of_step": ITERS * look_avg / (ITERS * look_avg + build_avg)},
         "build(pack+tcgen05)": {"avg_ms": build_avg, "GB/s": build_gbs, "frac_hbm": build_gbs / pk["hbm_gbs"], "TFLOP/s": build_tf,
-                                "frac_tensor": build_tf / pk["bf16_tflops_sustained"], "share_of_step": build_avg / (ITERS * look_avg + build_avg),
-                                "write_only_hbm_GB/s_measured": wr_gbs, "frac_of_write_only": build_gbs / wr_gbs},
+                                "frac_tensor": build_tf / pk["bf16_tflops_sustained"], "share_of_step": build_avg / (ITERS * look_avg + build_avg)},
     }
 
-    # ---- end to end through the public API from pinned host buffers
-    e2e = None
+    # ---- the lookup with fp16 output (what --mixed_precision callers get), same pyramid, as a third roofline object
     with torch.no_grad():
-        Be = min(B, args.e2e_batch)
+        blk16 = R.CorrBlock(f1, f2, LEVELS, RADIUS, storage=args.storage, math=args.math, out_dtype=torch.float16)
+        for c in coords[:3]:
+            blk16(c)
+        torch.cuda.synchronize()
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(ITERS + 1)]
+        ev[0].record(stream)
+        for i, c in enumerate(coords):
+            blk16(c)
+            ev[i + 1].record(stream)
+        torch.cuda.synchronize()
+        l16_ms = statistics.mean(ev[i].elapsed_time(ev[i + 1]) for i in range(ITERS))
+        l16_bytes = B * N * (LEVELS * (2 * RADIUS + 2) ** 2 * es + 8 + LEVELS * (2 * RADIUS + 1) ** 2 * 2)
+        roof_l16 = {"kernel": "lookup_fwd_kernel<fp16 out>", "bound": "hbm", "achieved": l16_bytes / l16_ms / 1e6,
+                    "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": l16_bytes / l16_ms / 1e6 / pk["hbm_gbs"],
+                    "traffic": ncu_traffic("lookup_fwd_kernel_f16out", B, args.storage), "peak_source": pk["source"],
+                    "algorithmic_bytes_per_launch": l16_bytes, "avg_launch_ms": l16_ms}
+        del blk16
+
+    # ---- parity of the timed configuration itself: 1 000 random outputs of the last lookup of a 64-pair step against
+    # the fp32 on-the-fly block (another kernel, fp32 FMA, no stored volume) on the same inputs, outside the timed region
+    with torch.no_grad():
+        out = step()
+        ref = R.AlternateCorrBlock(f1, f2, LEVELS, RADIUS, math="fp32")(coords[-1])
+        gsel = torch.Generator(device="cpu").manual_seed(5)
+        idx = torch.randint(0, out.numel(), (1000,), generator=gsel).to(device)
+        a, r_ = out.reshape(-1)[idx].double(), ref.reshape(-1)[idx].double()
+        err = (a - r_).abs()
+        floor = 3.0       # 3 rms(volume): N(0,1) features give a unit-variance volume (tests/test_gpu_parity.py: bf16_floor)
+        parity = {"checked": 1000, "against": "AlternateCorrBlock(math='fp32') on the same inputs",
+                  "max_rel_err_with_floor": float((err / (r_.abs() + floor)).max()),
+                  "share_within_plain_1e-2_relative": float((err <= 1e-2 * r_.abs()).double().mean()),
+                  "max_abs_err": float(err.max()), "tolerance": "1e-2 * (|ref| + 3 rms(volume)) for a bf16 volume"}
+        del out, ref
+
+    # ---- end to end through the public API from pinned host buffers: the SAME step as `value` (B pairs per GPU)
+    e2e = None
+    e2e16 = None
+    with torch.no_grad():
+        Be = B if args.e2e_batch <= 0 else min(B, args.e2e_batch)
         hf1, hf2 = f1[:Be].cpu().pin_memory(), f2[:Be].cpu().pin_memory()
         hcoords = [c[:Be].cpu().pin_memory() for c in coords]
         nch = LEVELS * (2 * RADIUS + 1) ** 2
-        houts = [torch.empty(Be, nch, H, W, dtype=torch.float32).pin_memory() for _ in range(ITERS)]
         copy_stream = torch.cuda.Stream(device)
 
-        def e2e_step():
-            d1 = hf1.to(device, non_blocking=True)
-            d2 = hf2.to(device, non_blocking=True)
-            blk = R.CorrBlock(d1, d2, LEVELS, RADIUS, storage=args.storage, math=args.math)
-            for i in range(ITERS):
-                c = hcoords[i].to(device, non_blocking=True)
-                o = blk(c)
-                ev = torch.cuda.Event(); ev.record(stream)
-                copy_stream.wait_event(ev)
-                with torch.cuda.stream(copy_stream):
-                    houts[i].copy_(o, non_blocking=True)
-                o.record_stream(copy_stream)
+        def run_e2e(out_dtype):
+            # Every lookup result goes to pinned host memory.  Two result buffers alternate, as in an application
+            # that consumes result i while result i+1 is on its way (12 distinct buffers of 584 MB per rank would
+            # pin 56 GB of host memory on an 8-GPU box); a buffer is reused only after its previous copy finished.
+            houts = [torch.empty(Be, nch, H, W, dtype=out_dtype).pin_memory() for _ in range(2)]
+            done = [None, None]
 
-        # Steps are pipelined as an application streaming batches would: the next step's uploads and build run
-        # while the previous step's last results are still on their way out (the copy stream keeps every copy
-        # into a host buffer in order); the clock stops only after the last result has landed.
-        e2e_step()
-        stream.wait_stream(copy_stream)
-        barrier()
-        t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
-        t0.record(stream)
-        for _ in range(args.e2e_steps):
+            def e2e_step():
+                d1 = hf1.to(device, non_blocking=True)
+                d2 = hf2.to(device, non_blocking=True)
+                blk = R.CorrBlock(d1, d2, LEVELS, RADIUS, storage=args.storage, math=args.math, out_dtype=out_dtype)
+                for i in range(ITERS):
+                    c = hcoords[i].to(device, non_blocking=True)
+                    o = blk(c)
+                    ev = torch.cuda.Event(); ev.record(stream)
+                    copy_stream.wait_event(ev)
+                    with torch.cuda.stream(copy_stream):
+                        houts[i & 1].copy_(o, non_blocking=True)     # stream order keeps the two buffers' copies apart
+                    o.record_stream(copy_stream)
+
+            # Steps are pipelined as an application streaming batches would: the next step's uploads and build run
+            # while the previous step's last results are still on their way out; the clock stops only after the
+            # last result has landed.
             e2e_step()
-        stream.wait_stream(copy_stream)
-        t1.record(stream)
-        barrier()
-        e2e_ms = t0.elapsed_time(t1)
-        if dist is not None:
-            tms = torch.tensor([e2e_ms], device=device)
-            dist.all_reduce(tms, op=dist.ReduceOp.MAX)
-            e2e_ms = float(tms.item())
-        e2e = {"value": world * Be * args.e2e_steps / (e2e_ms * 1e-3), "unit": "pairs/s",
-               "h2d_bytes_per_step": int(2 * Be * D * N * 4 + ITERS * Be * 2 * N * 4),
-               "d2h_bytes_per_step": int(ITERS * Be * nch * N * 4), "steps": args.e2e_steps,
-               "pairs_per_step": Be,
-               "api": "raft_stir_b200.CorrBlock(fmap1, fmap2)(coords) x12, pinned host in / pinned host out"}
+            stream.wait_stream(copy_stream)
+            barrier()
+            t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
+            t0.record(stream)
+            for _ in range(args.e2e_steps):
+                e2e_step()
+            stream.wait_stream(copy_stream)
+            t1.record(stream)
+            barrier()
+            my_ms = t0.elapsed_time(t1)
+            e2e_ms = my_ms
+            if dist is not None:
+                tms = torch.tensor([e2e_ms], device=device)
+                dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+                e2e_ms = float(tms.item())
+            d2h = int(ITERS * Be * nch * N * houts[0].element_size())
+            del houts, done
+            return {"value": world * Be * args.e2e_steps / (e2e_ms * 1e-3), "unit": "pairs/s",
+                    "h2d_bytes_per_step": int(2 * Be * D * N * 4 + ITERS * Be * 2 * N * 4),
+                    "d2h_bytes_per_step": d2h, "steps": args.e2e_steps, "pairs_per_step": Be,
+                    "d2h_gbs_per_rank": d2h * args.e2e_steps / (my_ms * 1e-3) / 1e9,
+                    "result_dtype": str(out_dtype).replace("torch.", ""),
+                    "api": "raft_stir_b200.CorrBlock(fmap1, fmap2)(coords) x12, pinned host in / pinned host out"}
+
+        e2e = run_e2e(torch.float32)
+        # the same with the block answering in fp16 (out_dtype=torch.float16, what --mixed_precision consumes): half
+        # the bytes on the PCIe link, which is what bounds this number (d2h_gbs_per_rank)
+        e2e16 = run_e2e(torch.float16)
+        e2e["fp16_results"] = {k: e2e16[k] for k in ("value", "d2h_bytes_per_step", "d2h_gbs_per_rank", "result_dtype")}
+        e2e["note"] = ("bounded by the device->host link: every pair returns 12 x 324 x 7040 outputs (109 MB fp32); "
+                       "d2h_gbs_per_rank is this rank's achieved result bandwidth")
 
     # ---- CPU baseline (rank 0, N = 1 only) and extras
     cpu = None
@@ -398,7 +462,8 @@ def main():
             "config": {"workload": WORKLOAD, "pairs_per_gpu_per_step": B, "volume_storage": args.storage,
                        "build_math": f"{args.math} tcgen05, fp32 accumulate", "l2": "working set per step (pyramid %.0f MB) exceeds the 126 MB L2" % (B * PYR_ELEMS * es / 1e6),
                        "parallelism": f"pairs sharded over {world} rank(s), no collective"},
-            "roofline": roof, "kernels": kernels, "cpu_baseline": cpu, "e2e": e2e,
+            "roofline": roof, "roofline_build": roof_build, "roofline_lookup_fp16_out": roof_l16, "kernels": kernels,
+            "parity_spot_check": parity, "cpu_baseline": cpu, "e2e": e2e,
             "gpu_launches": world * args.steps * (2 + ITERS), "clocks": clocks, "extras": extras,
         }
         print(json.dumps(line), flush=True)
@@ -430,7 +495,7 @@ def run_extras(R, device, args, pk):
             out["b1_build_fp32_simt_ms"] = timeit(lambda: R.CorrBlock(f1, f2, LEVELS, RADIUS, storage="fp32", math="fp32"), 3)
             out["b1_build_tf32_fp32_storage_ms"] = timeit(lambda: R.CorrBlock(f1, f2, LEVELS, RADIUS, storage="fp32", math="tf32"), 10)
             out["b1_build_bf16_fp32_storage_ms"] = timeit(lambda: R.CorrBlock(f1, f2, LEVELS, RADIUS, storage="fp32", math="bf16"), 10)
-            alt = R.AlternateCorrBlock(f1, f2, LEVELS, RADIUS)
+            alt = R.AlternateCorrBlock(f1, f2, LEVELS, RADIUS, math="fp32")
             out["b1_alt_lookup_ms"] = timeit(lambda: alt(coords[0]), 10)
             alt_tc = R.AlternateCorrBlock(f1, f2, LEVELS, RADIUS, math="bf16")
             out["b1_alt_tc_lookup_ms"] = timeit(lambda: alt_tc(coords[0]), 30)
@@ -469,7 +534,7 @@ def run_extras(R, device, args, pk):
             blk = R.CorrBlock(v1, v2, LEVELS, RADIUS, storage=args.storage, math=args.math)
             out["v1080_lookup_ms"] = timeit(lambda: blk(cv), 20)
             del blk
-            altv = R.AlternateCorrBlock(v1, v2, LEVELS, RADIUS)
+            altv = R.AlternateCorrBlock(v1, v2, LEVELS, RADIUS, math="fp32")
             out["v1080_alt_lookup_ms"] = timeit(lambda: altv(cv), 5)
             altv_tc = R.AlternateCorrBlock(v1, v2, LEVELS, RADIUS, math="bf16")
             out["v1080_alt_tc_lookup_ms"] = timeit(lambda: altv_tc(cv), 20)
@@ -504,6 +569,91 @@ def run_extras(R, device, args, pk):
             del fl, mk
     except Exception as e:  # extras must never sink the headline
         out["error"] = f"{type(e).__name__}: {e}"
+    try:
+        out.update(run_network_extras(R, device))
+    except Exception as e:
+        out["network_error"] = f"{type(e).__name__}: {str(e)[:300]}"
+    return out
+
+
+def run_network_extras(R, device):
+    """BASELINE configs 1 and 5 under the driver (part of the untimed CPU-baseline leg; rank 0, N = 1): the whole
+    RAFT-basic network with the reference's own sub-networks (traced to oracle/_ref/*.pt by oracle/make_ref_modules.py,
+    random-init weights, fp32) around (a) the reference CorrBlock's torch ops on this GPU and (b) this library.
+    Skipped when the traced networks are not on the machine."""
+    from oracle import raft_harness as Hn      # checker-side harness: control flow of RAFT.forward around the nets
+    if not Hn.available():
+        return {"network": "oracle/_ref/*.pt not present: configs 1 and 5 not run"}
+    out = {}
+    nets = Hn.load(device)
+
+    def timeit(fn, warm, reps):
+        for _ in range(warm):
+            r = fn()
+        torch.cuda.synchronize()
+        a = torch.cuda.Event(enable_timing=True); b = torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(reps):
+            r = fn()
+        b.record(); torch.cuda.synchronize()
+        return a.elapsed_time(b) / reps, r
+
+    # config 1: one 440x1024 pair, 12 iterations, test mode
+    g = torch.Generator(device="cpu").manual_seed(0)
+    im1 = (torch.rand(1, 3, 440, 1024, generator=g) * 255).to(device)
+    im2 = (torch.rand(1, 3, 440, 1024, generator=g) * 255).to(device)
+    with torch.no_grad():
+        timeit(lambda: Hn.raft_forward(nets, im1, im2, 12, R.CorrBlock), 2, 1)        # process warm-up
+        ms_ref, (_, up_ref) = timeit(lambda: Hn.raft_forward(nets, im1, im2, 12, Hn.TorchCorrBlock), 3, 5)
+        ms_our, (_, up) = timeit(lambda: Hn.raft_forward(nets, im1, im2, 12, R.CorrBlock), 3, 5)
+        ms_alt, (_, up_alt) = timeit(lambda: Hn.raft_forward(nets, im1, im2, 12, R.AlternateCorrBlock), 3, 5)
+        out["config1_raft_440x1024_12it"] = {
+            "torch_corrblock_ms": ms_ref, "this_library_bf16_ms": ms_our, "this_library_on_the_fly_ms": ms_alt,
+            "pairs_per_s": {"torch_corrblock": 1e3 / ms_ref, "this_library_bf16": 1e3 / ms_our},
+            "mean_epe_delta_px": torch.sqrt(((up - up_ref) ** 2).sum(1)).mean().item(),
+            "mean_epe_delta_px_on_the_fly": torch.sqrt(((up_alt - up_ref) ** 2).sum(1)).mean().item(),
+            "mean_flow_px": up_ref.norm(dim=1).mean().item(),
+            "note": "reference sub-networks (cuDNN, fp32) around the block; budget 0.01 px"}
+    del im1, im2
+
+    # config 5 on one GPU: training step, 10 pairs of 368x496, 12 iterations, sequence loss, AdamW, clip 1.0
+    import torch.nn as nn
+
+    class Net(nn.Module):
+        def __init__(self, nets, corr_cls, upsample_fn=None):
+            super().__init__()
+            self.fnet, self.cnet, self.update = nets
+            self.corr_cls, self.upsample_fn = corr_cls, upsample_fn
+
+        def forward(self, a, b):
+            return Hn.raft_forward_train((self.fnet, self.cnet, self.update), a, b, 12, self.corr_cls,
+                                         upsample_fn=self.upsample_fn)
+
+    Bt, Ht, Wt = 10, 368, 496
+    g = torch.Generator(device="cpu").manual_seed(100)
+    im1 = (torch.rand(Bt, 3, Ht, Wt, generator=g) * 255).to(device)
+    im2 = (torch.rand(Bt, 3, Ht, Wt, generator=g) * 255).to(device)
+    gt = (5 * torch.randn(Bt, 2, Ht, Wt, generator=g)).to(device)
+    valid = torch.ones(Bt, Ht, Wt, device=device)
+    res = {}
+    for name, cls, ups in (("torch_corrblock", Hn.TorchCorrBlock, None),
+                           ("this_library_block_and_upsampling", R.CorrBlock, R.upsample_flow)):
+        model = Net(Hn.load(device), cls, ups).to(device)
+        opt = torch.optim.AdamW(model.parameters(), lr=1e-5, weight_decay=1e-4)
+
+        def step():
+            opt.zero_grad(set_to_none=True)
+            loss = Hn.sequence_loss(model(im1, im2), gt, valid)
+            loss.backward()
+            torch.nn.utils.clip_grad_norm_(model.parameters(), 1.0)
+            opt.step()
+            return loss
+        ms, loss = timeit(step, 2, 3)
+        res[name] = {"ms_per_step": ms, "pairs_per_s": 1e3 * Bt / ms, "loss": float(loss.item())}
+        del model, opt
+        torch.cuda.empty_cache()
+    res["note"] = "one GPU, no DDP (tests/perf/train_step_bench.py runs the 8-GPU DistributedDataParallel form)"
+    out["config5_train_step_chairs_b10"] = res
     return out
 
 

@@ -59,7 +59,7 @@ with torch.no_grad():
         f2 = torch.randn(1, 256, H, W, generator=g).to(dev)
         coords = R.coords_grid(1, H, W, dev) + 5 * torch.randn(1, 2, H, W, generator=g).to(dev)
         ref = ref_block(f1, f2)
-        ours = R.AlternateCorrBlock(f1, f2, 4, 4)
+        ours = R.AlternateCorrBlock(f1, f2, 4, 4, math="fp32")
         ours_tc = R.AlternateCorrBlock(f1, f2, 4, 4, math="bf16")
         ms_ref, o_ref = timeit(lambda: ref(coords), 5)
         ms_ours, o_ours = timeit(lambda: ours(coords), 10)

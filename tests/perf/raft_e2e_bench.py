@@ -46,7 +46,7 @@ def main():
                       ("ours_tf32_build_fp16_volume", partial(R.CorrBlock, storage="fp16", math="tf32")),
                       ("ours_tf32_build_fp32_volume", partial(R.CorrBlock, storage="fp32", math="tf32")),
                       ("ours_fp32", partial(R.CorrBlock, storage="fp32", math="fp32")),
-                      ("ours_on_the_fly", R.AlternateCorrBlock),
+                      ("ours_on_the_fly", partial(R.AlternateCorrBlock, math="fp32")),
                       ("ours_on_the_fly_tensor_core", partial(R.AlternateCorrBlock, math="bf16")),
                       ("ours_on_the_fly_tensor_core_fp16_operands", partial(R.AlternateCorrBlock, math="fp16"))):
         ms, up = timeit(cls, 5)

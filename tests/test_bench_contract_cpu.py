@@ -18,7 +18,10 @@ def test_reference_arm_json_line():
               "scaling", "vs_baseline", "dtype", "data", "config", "cpu_baseline", "e2e"):
         assert k in d, k
     assert d["impl"] == "reference" and d["value"] > 0 and d["vs_baseline"] is None
-    assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1
+    # "reference" when oracle/stage_ref_python.py has staged the reference's own corr.py (build() does, where the
+    # checkout is mounted), else the torch port
+    staged = os.path.exists(os.path.join(ROOT, "oracle", "_ref", "refcore", "corr.py"))
+    assert d["cpu_baseline"]["kind"] == ("reference" if staged else "port") and d["cpu_baseline"]["cores"] >= 1
     assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0
     assert "workload" in d["config"]
 

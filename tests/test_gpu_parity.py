@@ -345,7 +345,7 @@ def test_training_accumulates_over_iterations():
 # ------------------------------------------------------------------ on-the-fly path
 @pytest.mark.parametrize("kind", KINDS)
 def test_alternate_block_matches_reference(golden, kind):
-    blk = R.AlternateCorrBlock(t(golden["fmap1"]), t(golden["fmap2"]), 4, int(golden["radius"]))
+    blk = R.AlternateCorrBlock(t(golden["fmap1"]), t(golden["fmap2"]), 4, int(golden["radius"]), math="fp32")
     out = blk(t(golden[f"coords_{kind}"]))
     ref = golden[f"out_{kind}"]
     assert tuple(out.shape) == ref.shape and out.dtype == torch.float32
@@ -375,7 +375,7 @@ def test_alternate_equals_default_at_sintel_shape():
     f1 = t(rng.standard_normal((B, D, H, W)).astype(np.float32))
     f2 = t(rng.standard_normal((B, D, H, W)).astype(np.float32))
     c = R.coords_grid(B, H, W, dev()) + 5 * torch.randn(B, 2, H, W, device=dev())
-    a = R.AlternateCorrBlock(f1, f2, 4, 4)(c)
+    a = R.AlternateCorrBlock(f1, f2, 4, 4, math="fp32")(c)
     d = R.CorrBlock(f1, f2, 4, 4, storage="fp32", math="fp32")(c)
     rel_close(a.cpu().numpy(), d.cpu().numpy(), 1e-4, "alt vs default, fp32")
     h = R.CorrBlock(f1, f2, 4, 4)(c)
@@ -521,7 +521,7 @@ def test_video_shape_beyond_32bit_offsets():
     blk = R.CorrBlock(f1, f2, 4, 4)
     assert blk.layout.total_elems > 2 ** 31
     got = blk(c)
-    ref = R.AlternateCorrBlock(f1, f2, 4, 4)(c)
+    ref = R.AlternateCorrBlock(f1, f2, 4, 4, math="fp32")(c)
     rel_close(got.cpu().numpy(), ref.cpu().numpy(), 1e-2, "1080p, bf16 volume vs on-the-fly fp32",
               floor=bf16_floor(f1.cpu().numpy(), f2.cpu().numpy()))
     # the last query of the last pair sits at the far end of every level
@@ -540,9 +540,9 @@ def test_alternate_tensor_core_fp16_operands():
         coords = (O.coords_grid(B, H, W) + rng.normal(0, 4, (B, 2, H, W))).astype(np.float32)
         got = R.AlternateCorrBlock(t(f1), t(f2), 4, r, math="fp16")(t(coords)).cpu().numpy()
         n = (2 * r + 1) ** 2
-        ref16 = R.AlternateCorrBlock(t(fp16_round(f1)), t(fp16_round(f2)), 4, r)(t(coords)).cpu().numpy()
+        ref16 = R.AlternateCorrBlock(t(fp16_round(f1)), t(fp16_round(f2)), 4, r, math="fp32")(t(coords)).cpu().numpy()
         rel_close(got[:, :n], ref16[:, :n], 2e-5, f"alt fp16 operands {shape} level 0")
-        ref = R.AlternateCorrBlock(t(f1), t(f2), 4, r)(t(coords)).cpu().numpy()
+        ref = R.AlternateCorrBlock(t(f1), t(f2), 4, r, math="fp32")(t(coords)).cpu().numpy()
         rel_close(got, ref, 1e-3, f"alt fp16 operands {shape} vs fp32", floor=bf16_floor(f1, f2))
     with pytest.raises(RuntimeError):
         R.AlternateCorrBlock(t(f1), t(f2), 4, 4, math="fp8")
@@ -577,7 +577,7 @@ def test_alternate_tensor_core_matches_fp32_path(shape, kind):
     else:
         coords = grid + np.array([W - 6.5, -(H - 5.25)]).reshape(1, 2, 1, 1) * (grid[:, :1] > W / 2)
     coords = coords.astype(np.float32)
-    ref = R.AlternateCorrBlock(t(f1), t(f2), 4, r)(t(coords))
+    ref = R.AlternateCorrBlock(t(f1), t(f2), 4, r, math="fp32")(t(coords))
     got = R.AlternateCorrBlock(t(f1), t(f2), 4, r, math="bf16")(t(coords))
     assert got.shape == ref.shape
     n = (2 * r + 1) ** 2

@@ -80,8 +80,22 @@ def test_flow_with_fp32_volume(reference_run):
 
 def test_flow_with_on_the_fly_correlation(reference_run):
     nets, im1, im2, low, up = reference_run
-    _, got = Hn.raft_forward(nets, im1, im2, iters=12, corr_cls=R.AlternateCorrBlock)
+    _, got = Hn.raft_forward(nets, im1, im2, iters=12, corr_cls=partial(R.AlternateCorrBlock, math="fp32"))
     assert _epe(got, up) <= 1e-3
+
+
+def test_flow_with_on_the_fly_correlation_default_settings(reference_run):
+    """AlternateCorrBlock as a user swapping the two names gets it: D = 256 -> the tensor-core path (bf16 operands)."""
+    nets, im1, im2, low, up = reference_run
+    blocks = []
+
+    def make(f1, f2, **kw):
+        blocks.append(R.AlternateCorrBlock(f1, f2, **kw))
+        return blocks[-1]
+    _, got = Hn.raft_forward(nets, im1, im2, iters=12, corr_cls=make)
+    assert blocks and blocks[0].math == "bf16"
+    d = _epe(got, up)
+    assert d <= 0.01, f"mean EPE delta {d:.5f} px > 0.01 px"
 
 
 def test_flow_with_on_the_fly_correlation_on_tensor_cores(reference_run):

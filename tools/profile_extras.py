@@ -25,7 +25,7 @@ with torch.no_grad():
     a1 = torch.randn(1, D, 55, 128, generator=g).to(dev)
     a2 = torch.randn(1, D, 55, 128, generator=g).to(dev)
     c = R.coords_grid(1, 55, 128, dev) + 5 * torch.randn(1, 2, 55, 128, generator=g).to(dev)
-    alt = R.AlternateCorrBlock(a1, a2, 4, 4)
+    alt = R.AlternateCorrBlock(a1, a2, 4, 4, math="fp32")
     for _ in range(2):
         alt(c)
 torch.cuda.synchronize()
