@@ -59,16 +59,28 @@ def ncu_traffic(kernel, batch, storage):
 
 
 def write_only_gbs(device):
-    """HBM bandwidth of a pure write stream, measured live with cudaMemsetAsync over 2 GiB (torch's zero_ is that
-    call).  Round 1 quoted torch's fill kernel here (3.9 TB/s) as "the" write-only ceiling; tools/store_probe.cu
+    """HBM bandwidth of a pure write stream, measured live with cudaMemsetAsync over 2 GiB (called through
+    libcudart; torch's zero_ / fill_ kernels stop at 3.9 TB/s).  Round 1 quoted torch's fill kernel here (3.9 TB/s) as "the" write-only ceiling; tools/store_probe.cu
     (profiles/r2b_store_probe.jsonl, hand-written stores) shows that was the fill kernel's limit, not the memory's:
     memset 7.3 TB/s, bulk shared->global copies 6.4 TB/s, the build's own access pattern (256 contiguous bytes per
     query row per visit) 5.9 TB/s with plain 16-byte stores."""
+    import ctypes
     buf = torch.empty(1 << 31, dtype=torch.uint8, device=device)
+    try:
+        rt = ctypes.CDLL("libcudart.so.12")
+        rt.cudaMemsetAsync.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_size_t, ctypes.c_void_p]
+        st = torch.cuda.current_stream().cuda_stream
+
+        def fill():
+            if rt.cudaMemsetAsync(buf.data_ptr(), 0, 1 << 31, st) != 0:
+                raise RuntimeError("cudaMemsetAsync failed")
+    except OSError:          # no libcudart on the loader path: torch's fill kernel (slower than the memory)
+        def fill():
+            buf.zero_()
     best = 1e9
     for i in range(5):
         e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
-        e0.record(); buf.zero_(); e1.record(); torch.cuda.synchronize()
+        e0.record(); fill(); e1.record(); torch.cuda.synchronize()
         if i:
             best = min(best, e0.elapsed_time(e1))
     return (1 << 31) / best / 1e6
@@ -648,7 +660,8 @@ def run_network_extras(R, device):
             torch.nn.utils.clip_grad_norm_(model.parameters(), 1.0)
             opt.step()
             return loss
-        ms, loss = timeit(step, 2, 3)
+        torch.cuda.empty_cache()
+        ms, loss = timeit(step, 3, 3)
         res[name] = {"ms_per_step": ms, "pairs_per_s": 1e3 * Bt / ms, "loss": float(loss.item())}
         del model, opt
         torch.cuda.empty_cache()

@@ -28,7 +28,7 @@ extern "C" {
 #define RC_API
 #endif
 
-#define RC_ABI_VERSION 4
+#define RC_ABI_VERSION 5
 #define RC_MAX_LEVELS 6
 
 /* error codes */
@@ -138,6 +138,24 @@ RC_API int rc_build_pyramid_static(const float *fmap1, const float *fmap2, int B
                                    int num_levels, int vol_dtype, void *pyramid, rc_stream_t stream);
 
 /*
+ * The same build for a caller that already holds 16-bit channels-last features (SURVEY.md section 8(f) row 4:
+ * the reference's encoder ends in a 1x1 convolution, core/extractor.py:144,184; run in channels_last bf16 it
+ * emits exactly this layout, and the fp32 round trip of core/raft.py:99-103 plus the repack disappear).
+ *   fmap1_nhwc16, fmap2_nhwc16 : bf16 or fp16 [B, H, W, D] contiguous, UNSCALED, 128-byte aligned, D % 64 == 0
+ *   operand_dtype              : RC_VOL_BF16 or RC_VOL_F16 (the element type of the two buffers = the MMA operands)
+ * No workspace: fmap1 is read as [B*N, D] rows; the 8 x 32 spatial blocks of fmap2 that form one GEMM tile are
+ * cut out of the NHWC tensor by a 4-D TMA box (rows outside the map arrive as zeros), and 1/sqrt(D) is applied
+ * to the fp32 accumulators.  Same result as rc_build_pyramid on the same 16-bit values.
+ * rc_pack_features_nhwc16 produces such buffers from the fp32 NCHW maps (one transposing cast per map), e.g. to
+ * share one packed copy between this build and rc_alt_lookup_fwd_tc (whose fmap1_16 is this fmap1_nhwc16).
+ */
+RC_API int rc_pack_features_nhwc16(const float *fmap1, const float *fmap2, int B, int D, int H, int W,
+                            int operand_dtype, void *fmap1_nhwc16, void *fmap2_nhwc16, rc_stream_t stream);
+RC_API int rc_build_pyramid_nhwc16(const void *fmap1_nhwc16, const void *fmap2_nhwc16, int operand_dtype, int B,
+                            int D, int H, int W, int num_levels, int vol_dtype, void *pyramid,
+                            rc_stream_t stream);
+
+/*
  * Windowed bilinear lookup over all levels in one launch.  Replaces
  * CorrBlock.__call__ (core/corr.py:29-50) together with bilinear_sampler /
  * F.grid_sample(align_corners=True, zeros padding) (core/utils/utils.py:57-65).
@@ -145,6 +163,8 @@ RC_API int rc_build_pyramid_static(const float *fmap1, const float *fmap2, int B
  *   out    : fp32 [B, num_levels*(2r+1)^2, H, W]; channel l*(2r+1)^2 + i*(2r+1) + j
  *            samples level l at (x/2^l + i - r, y/2^l + j - r)
  *   radius : 1..4
+ * Finite coordinates far outside the map give zeros (zeros padding); NaN or infinite coordinates give NaN in
+ * every sample of that query, as the reference's grid_sample does (the on-the-fly entry points do the same).
  */
 RC_API int rc_lookup_fwd(const void *pyramid, int vol_dtype, const float *coords, int B, int H, int W,
                   int num_levels, int radius, float *out, rc_stream_t stream);

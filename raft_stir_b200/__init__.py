@@ -6,9 +6,9 @@ hand-written CUDA kernels behind the C ABI declared in include/raft_corr.h.
 There is no CPU path: constructing a block without the compiled library or
 without a CUDA tensor raises.
 """
-from .corr import AlternateCorrBlock, CorrBlock, coords_grid, install_into  # noqa: F401
+from .corr import AlternateCorrBlock, CorrBlock, coords_grid, install_into, pack_features  # noqa: F401
 from . import alt_cuda_corr  # noqa: F401
 from .upsample import upflow8, upsample_flow  # noqa: F401
 
-__all__ = ["CorrBlock", "AlternateCorrBlock", "alt_cuda_corr", "coords_grid", "install_into", "upsample_flow",
+__all__ = ["CorrBlock", "AlternateCorrBlock", "alt_cuda_corr", "coords_grid", "install_into", "pack_features", "upsample_flow",
            "upflow8"]

@@ -16,6 +16,7 @@ from __future__ import annotations
 
 import ctypes as C
 import os
+import weakref
 from typing import List, Optional
 
 import torch
@@ -76,6 +77,33 @@ def coords_grid(batch: int, ht: int, wd: int, device) -> torch.Tensor:
     return torch.stack([xs, ys], dim=0).float()[None].repeat(batch, 1, 1, 1)
 
 
+_OP16 = {torch.bfloat16: _lib.RC_VOL_BF16, torch.float16: _lib.RC_VOL_F16}
+
+
+def _is_nhwc16(t) -> bool:
+    return (isinstance(t, torch.Tensor) and t.is_cuda and t.dtype in _OP16 and t.dim() == 4
+            and t.shape[1] % 64 == 0)
+
+
+def pack_features(fmap1: torch.Tensor, fmap2: torch.Tensor, dtype: torch.dtype = torch.bfloat16):
+    """fp32 NCHW feature maps -> 16-bit channels-last tensors (logical shape [B, D, H, W], memory NHWC), the form
+    `CorrBlock` consumes without any repack (rc_build_pyramid_nhwc16) and the form a channels_last bf16 encoder would
+    emit directly (core/extractor.py:144,184 -> core/raft.py:99-103).  One transposing cast per map."""
+    if dtype not in _OP16:
+        raise RaftCorrError(f"dtype={dtype!r}: expected torch.bfloat16 or torch.float16")
+    f1 = _require_cuda_f32(fmap1.detach(), "fmap1")
+    f2 = _require_cuda_f32(fmap2.detach(), "fmap2")
+    if f1.shape != f2.shape or f1.dim() != 4:
+        raise RaftCorrError(f"fmap shapes {tuple(f1.shape)} vs {tuple(f2.shape)}: expected equal [B,D,H,W]")
+    B, D, H, W = (int(v) for v in f1.shape)
+    o1 = torch.empty((B, D, H, W), dtype=dtype, device=f1.device, memory_format=torch.channels_last)
+    o2 = torch.empty((B, D, H, W), dtype=dtype, device=f1.device, memory_format=torch.channels_last)
+    with _guard(f1.device):
+        check(_lib.lib().rc_pack_features_nhwc16(f1.data_ptr(), f2.data_ptr(), B, D, H, W, _OP16[dtype], o1.data_ptr(),
+                                                 o2.data_ptr(), _stream(f1)), "rc_pack_features_nhwc16")
+    return o1, o2
+
+
 class _BuildFn(torch.autograd.Function):
     """Autograd node of the volume build.  Its output is a one-element token
     that every lookup takes as an input, so autograd runs this backward once,
@@ -84,14 +112,20 @@ class _BuildFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, fmap1, fmap2, blk):
         blk._build(fmap1, fmap2)
-        ctx.blk = blk
+        # weak: the block owns the token whose grad_fn is this node; a strong reference back would make a cycle that
+        # only the cyclic GC frees, keeping a step's pyramid and gradient pyramid (GBs at training batch sizes) alive.
+        # Every lookup node holds the block strongly, so it lives as long as any lookup output is part of the graph.
+        ctx.blk_ref = weakref.ref(blk)
         ctx.save_for_backward(fmap1, fmap2)
         return torch.zeros(1, device=fmap1.device, dtype=torch.float32)
 
     @staticmethod
     def backward(ctx, _token_grad):
         fmap1, fmap2 = ctx.saved_tensors
-        d1, d2 = ctx.blk._build_backward(fmap1, fmap2)
+        blk = ctx.blk_ref()
+        if blk is None:                    # no lookup output survived: nothing flowed into the volume
+            return torch.zeros_like(fmap1), torch.zeros_like(fmap2), None
+        d1, d2 = blk._build_backward(fmap1, fmap2)
         return d1, d2, None
 
 
@@ -128,6 +162,10 @@ class CorrBlock:
              fp16 is for inference under fp16 autocast (--mixed_precision): the update block's first convolution
              would cast the fp32 result itself; the lookup then writes half the bytes and the cast pass disappears.
     Defaults can be set with RAFT_CORR_STORAGE / RAFT_CORR_MATH / RAFT_CORR_OUT (fp32|fp16).
+
+    Features that are already 16-bit (torch.bfloat16 / torch.float16, D % 64 == 0, no gradient wanted) -- what an
+    encoder run in channels_last bf16 hands over, or `pack_features` -- are consumed in place: no fp32 round trip, no
+    repack, no workspace (rc_build_pyramid_nhwc16); `math` is then the tensors' own type.
     """
 
     def __init__(self, fmap1, fmap2, num_levels: int = 4, radius: int = 4, *,
@@ -147,8 +185,15 @@ class CorrBlock:
         self.math = _MATH[math]
         _lib.lib()   # fail loudly before touching tensors if the extension is missing
 
-        f1 = _require_cuda_f32(fmap1, "fmap1")
-        f2 = _require_cuda_f32(fmap2, "fmap2")
+        self._nhwc16 = (_is_nhwc16(fmap1) and _is_nhwc16(fmap2) and fmap1.dtype == fmap2.dtype
+                        and not (torch.is_grad_enabled() and (fmap1.requires_grad or fmap2.requires_grad)))
+        if self._nhwc16:
+            f1 = fmap1.detach().contiguous(memory_format=torch.channels_last)     # no copy when the encoder ran channels_last
+            f2 = fmap2.detach().contiguous(memory_format=torch.channels_last)
+            self.math = _lib.RC_MATH_BF16 if f1.dtype is torch.bfloat16 else _lib.RC_MATH_F16
+        else:
+            f1 = _require_cuda_f32(fmap1, "fmap1")
+            f2 = _require_cuda_f32(fmap2, "fmap2")
         if f1.shape != f2.shape or f1.dim() != 4:
             raise RaftCorrError(f"fmap shapes {tuple(f1.shape)} vs {tuple(f2.shape)}: expected equal [B,D,H,W]")
         if f1.device != f2.device:
@@ -170,6 +215,14 @@ class CorrBlock:
         L = _lib.lib()
         lay = self.layout
         self._buf = torch.empty(int(lay.total_elems), dtype=_TORCH_DT[self.vol_dtype], device=self.device)
+        if self._nhwc16:
+            with _guard(self.device):
+                check(L.rc_build_pyramid_nhwc16(f1.data_ptr(), f2.data_ptr(), _OP16[f1.dtype], self.B, self.D, self.H,
+                                                self.W, self.num_levels, self.vol_dtype, self._buf.data_ptr(),
+                                                _stream(f1)), "rc_build_pyramid_nhwc16")
+            f1.record_stream(torch.cuda.current_stream(self.device))
+            f2.record_stream(torch.cuda.current_stream(self.device))
+            return
         ws_bytes = int(L.rc_build_workspace_bytes(self.B, self.D, self.H, self.W, self.math))
         if ws_bytes < 0:
             raise RaftCorrError("rc_build_workspace_bytes rejected the sizes")

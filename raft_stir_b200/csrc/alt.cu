@@ -78,7 +78,9 @@ alt_fwd_kernel(const float *__restrict__ fmap1, const float *__restrict__ fmap2,
     const float fx = floorf(cx), fy = floorf(cy);
     const int x0 = sane ? (int)fx - R : -(1 << 24);
     const int y0 = sane ? (int)fy - R : -(1 << 24);
-    const float ax = sane ? cx - fx : 0.f, ay = sane ? cy - fy : 0.f;
+    // NaN / infinite coordinates: NaN in every sample of the query (what the reference kernel's dx = x - floor(x) gives)
+    const float off = ((cx - cx == 0.f) && (cy - cy == 0.f)) ? 0.f : __int_as_float(0x7fc00000);
+    const float ax = sane ? cx - fx : off, ay = sane ? cy - fy : off;
 
     // this query's feature vector: lane holds channels lane*4 + 128*k .. +3
     float4 a[ALT_KV];
@@ -171,7 +173,9 @@ alt_bwd_kernel(const float *__restrict__ fmap1, const float *__restrict__ fmap2,
     const float fx = floorf(cx), fy = floorf(cy);
     const int x0 = sane ? (int)fx - R : -(1 << 24);
     const int y0 = sane ? (int)fy - R : -(1 << 24);
-    const float ax = sane ? cx - fx : 0.f, ay = sane ? cy - fy : 0.f;
+    // NaN / infinite coordinates: NaN in every sample of the query (what the reference kernel's dx = x - floor(x) gives)
+    const float off = ((cx - cx == 0.f) && (cy - cy == 0.f)) ? 0.f : __int_as_float(0x7fc00000);
+    const float ax = sane ? cx - fx : off, ay = sane ? cy - fy : off;
 
     const float *g = corr_grad + (((size_t)b * Nc + n) * NW * NW) * N1 + q;
     for (int o = lane; o < NW * NW; o += 32) gout[warp][o] = __ldg(g + (size_t)o * N1);

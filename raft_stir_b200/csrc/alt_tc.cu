@@ -63,7 +63,10 @@ __device__ __forceinline__ bool window_at_level(float cxf, float cyf, int l, int
   const float inv = __int_as_float((127 - l) << 23);
   const float cx = cxf * inv, cy = cyf * inv;
   x0 = 0; y0 = 0; ax = 0.f; ay = 0.f;
-  if (!(fabsf(cx) < 1.0e7f && fabsf(cy) < 1.0e7f)) return false;
+  if (!(fabsf(cx) < 1.0e7f && fabsf(cy) < 1.0e7f)) {
+    if (!((cx - cx == 0.f) && (cy - cy == 0.f))) ax = ay = __int_as_float(0x7fc00000);   // NaN / Inf coordinates -> NaN samples
+    return false;
+  }
   const float fx = floorf(cx), fy = floorf(cy);
   x0 = (int)fx - R; y0 = (int)fy - R;
   ax = cx - fx; ay = cy - fy;
@@ -133,6 +136,8 @@ alt_tc_fwd_kernel(const __grid_constant__ AtcMaps maps, const float *__restrict_
         x0 = (int)fx - R; y0 = (int)fy - R;
         ax = cx - fx; ay = cy - fy;
         relevant = x0 + T > 0 && x0 < Wl && y0 + T > 0 && y0 < Hl;     // the window meets the map
+      } else if (!((cx - cx == 0.f) && (cy - cy == 0.f))) {
+        ax = ay = __int_as_float(0x7fc00000);                          // NaN / Inf coordinates -> NaN samples
       }
     }
     if (relevant) {

@@ -161,7 +161,7 @@ int rc_build_pyramid(const float *fmap1, const float *fmap2, int B, int D, int H
   void *f2p = (char *)workspace + round_up64((int64_t)B * H * W * D * es, 1024);
   r = launch_pack(fmap1, fmap2, B, D, H, W, math, f1p, f2p, s);
   if (r) return r;
-  return launch_build_tc(f1p, f2p, B, D, H, W, lay, vol_dtype, math, pyramid, s);
+  return launch_build_tc(f1p, f2p, B, D, H, W, lay, vol_dtype, math, 0, pyramid, s);
 }
 
 int rc_build_pyramid_static(const float *fmap1, const float *fmap2, int B, int D, int H, int W,
@@ -189,7 +189,33 @@ int rc_build_pyramid_static(const float *fmap1, const float *fmap2, int B, int D
   void *f2p = (char *)scratch + round_up64((int64_t)B * H * W * D * 2, 1024);
   r = launch_pack(fmap1, fmap2, B, D, H, W, RC_MATH_BF16, f1p, f2p, s);
   if (r) return r;
-  return launch_build_tc(f1p, f2p, B, D, H, W, lay, vol_dtype, RC_MATH_BF16, pyramid, s);
+  return launch_build_tc(f1p, f2p, B, D, H, W, lay, vol_dtype, RC_MATH_BF16, 0, pyramid, s);
+}
+
+int rc_pack_features_nhwc16(const float *fmap1, const float *fmap2, int B, int D, int H, int W, int operand_dtype,
+                            void *fmap1_nhwc16, void *fmap2_nhwc16, rc_stream_t stream) {
+  RC_REQUIRE(fmap1 && fmap2 && fmap1_nhwc16 && fmap2_nhwc16, "rc_pack_features_nhwc16: NULL pointer");
+  RC_REQUIRE(B >= 1 && B <= 65535 && D >= 2 && D % 2 == 0 && H >= 1 && W >= 1, "rc_pack_features_nhwc16: bad sizes B=%d D=%d H=%d W=%d", B, D, H, W);
+  RC_REQUIRE(operand_dtype == RC_VOL_BF16 || operand_dtype == RC_VOL_F16, "rc_pack_features_nhwc16: operand_dtype %d", operand_dtype);
+  return launch_pack_nhwc16(fmap1, fmap2, B, D, H, W, operand_dtype == RC_VOL_F16, fmap1_nhwc16, fmap2_nhwc16,
+                            (cudaStream_t)stream);
+}
+
+int rc_build_pyramid_nhwc16(const void *fmap1_nhwc16, const void *fmap2_nhwc16, int operand_dtype, int B, int D, int H,
+                            int W, int num_levels, int vol_dtype, void *pyramid, rc_stream_t stream) {
+  RC_REQUIRE(fmap1_nhwc16 && fmap2_nhwc16 && pyramid, "rc_build_pyramid_nhwc16: NULL pointer");
+  RC_REQUIRE(operand_dtype == RC_VOL_BF16 || operand_dtype == RC_VOL_F16, "rc_build_pyramid_nhwc16: operand_dtype %d", operand_dtype);
+  RC_REQUIRE(D >= 64 && D % 64 == 0, "rc_build_pyramid_nhwc16: D=%d must be a multiple of 64", D);
+  RC_REQUIRE(((uintptr_t)fmap1_nhwc16 & 127) == 0 && ((uintptr_t)fmap2_nhwc16 & 127) == 0,
+             "rc_build_pyramid_nhwc16: feature buffers must be 128-byte aligned");
+  RC_REQUIRE(((uintptr_t)pyramid & 255) == 0, "pyramid must be 256-byte aligned");
+  rc_layout lay;
+  int r = make_layout(B, H, W, num_levels, vol_dtype, &lay);
+  if (r) return r;
+  r = check_tc_limits("rc_build_pyramid_nhwc16", D, num_levels);
+  if (r) return r;
+  return launch_build_tc(fmap1_nhwc16, fmap2_nhwc16, B, D, H, W, lay, vol_dtype,
+                         operand_dtype == RC_VOL_F16 ? RC_MATH_F16 : RC_MATH_BF16, 1, pyramid, (cudaStream_t)stream);
 }
 
 int rc_lookup_fwd(const void *pyramid, int vol_dtype, const float *coords, int B, int H, int W,

@@ -49,6 +49,7 @@ constexpr int GW = TB_W / 2;           // block columns per epilogue group (16)
 struct TcParams {
   int B, N, MT, NT, nbx, KB, num_levels, stages;
   int group_pairs, num_groups;      // pairs processed together (see TileWalk)
+  int b_nhwc;                       // fmap2 operand is plain NHWC [B][H][W][D]: its 8x32 blocks are cut by a 4-D TMA box
   uint32_t idesc;                   // instruction descriptor (operand format: bf16, f16 or tf32)
   float scale;                      // what is left of 1/sqrt(D) after the pack's exact power-of-two part
   // pyramid geometry (levels >= num_levels are unused)
@@ -263,7 +264,10 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
           mbar_wait(bar_b_empty + 8 * st, ph ^ 1);
           mbar_expect_tx(bar_b_full + 8 * st, SLOT);
           if (TF32) tma_load_3d(sB + st * SLOT, &map_a, bar_b_full + 8 * st, kb * BKE, m * BM, b, pol_in);
-          tma_load_3d(sB + st * SLOT + (TF32 ? A_KB_BYTES : 0), &map_b, bar_b_full + 8 * st, kb * BKE, n * BN, b, pol_in);
+          if (!TF32 && p.b_nhwc)     // box (64 d, 32 x, 8 y): lands in the block order the pack would have written; outside the map: zeros
+            tma_load_4d_hint(sB + st * SLOT, &map_b, bar_b_full + 8 * st, kb * BKE, bx * TB_W, by * TB_H, b, pol_in);
+          else
+            tma_load_3d(sB + st * SLOT + (TF32 ? A_KB_BYTES : 0), &map_b, bar_b_full + 8 * st, kb * BKE, n * BN, b, pol_in);
           if (++st == (uint32_t)p.stages) { st = 0; ph ^= 1; }
         }
       }
@@ -539,7 +543,7 @@ int encode(CUtensorMap *map, CUtensorMapDataType dt, int rank, const void *base,
 
 template <typename VolT, bool TF32>
 int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, const rc_layout &lay,
-               VolT *pyr, bool half_operands, cudaStream_t s) {
+               VolT *pyr, bool half_operands, bool nhwc, cudaStream_t s) {
   constexpr int BKE = TF32 ? BK / 2 : BK;
   constexpr int OPB = TF32 ? 4 : 2;                 // operand bytes per element
   constexpr size_t SLOT = TF32 ? A_KB_BYTES + B_ST_BYTES : B_ST_BYTES;
@@ -566,6 +570,12 @@ int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, con
   p.num_levels = L;
   float pre_scale = 1.f;
   split_scale(D, &pre_scale, &p.scale);      // pre_scale was applied to fmap1 by the pack
+  if (nhwc) p.scale = 1.0f / sqrtf((float)D);   // caller's features: unscaled, the whole factor goes to the epilogue
+  p.b_nhwc = nhwc ? 1 : 0;
+  if (nhwc && (TF32 || D % BKE != 0)) {
+    set_error("NHWC feature input needs 16-bit operands and D %% 64 == 0 (got D = %d)", D);
+    return RC_EINVAL;
+  }
   for (int l = 0; l < 4; ++l) {
     const bool on = l < L;
     p.Hl[l] = on ? lay.H[l] : 0;
@@ -611,7 +621,13 @@ int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, con
     int r = encode(&ma, op_type, 3, f1p, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B, "fmap1");
     if (r) return r;
   }
-  {
+  if (nhwc) {
+    cuuint64_t dims[4] = {(cuuint64_t)D, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
+    cuuint64_t str[3] = {(cuuint64_t)D * OPB, (cuuint64_t)W * D * OPB, (cuuint64_t)H * W * D * OPB};
+    cuuint32_t box[4] = {BKE, TB_W, TB_H, 1};
+    int r = encode(&mb, op_type, 4, f2p, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B, "fmap2 (NHWC)");
+    if (r) return r;
+  } else {
     cuuint64_t dims[3] = {(cuuint64_t)D, (cuuint64_t)rows2, (cuuint64_t)B};
     cuuint64_t str[2] = {(cuuint64_t)D * OPB, (cuuint64_t)rows2 * D * OPB};
     cuuint32_t box[3] = {BKE, BN, 1};
@@ -637,19 +653,20 @@ int encode_tiled(CUtensorMap *map, CUtensorMapDataType dt, int rank, const void 
 }
 
 int launch_build_tc(const void *f1p, const void *f2p, int B, int D, int H, int W, const rc_layout &lay,
-                    int vol_dtype, int math, void *pyramid, cudaStream_t s) {
+                    int vol_dtype, int math, int nhwc, void *pyramid, cudaStream_t s) {
+  const bool nh = nhwc != 0;
   if (math == RC_MATH_TF32)
-    return vol_dtype == RC_VOL_BF16  ? build_tc_t<__nv_bfloat16, true>(f1p, f2p, B, D, H, W, lay, (__nv_bfloat16 *)pyramid, false, s)
-           : vol_dtype == RC_VOL_F16 ? build_tc_t<__half, true>(f1p, f2p, B, D, H, W, lay, (__half *)pyramid, false, s)
-                                     : build_tc_t<float, true>(f1p, f2p, B, D, H, W, lay, (float *)pyramid, false, s);
+    return vol_dtype == RC_VOL_BF16  ? build_tc_t<__nv_bfloat16, true>(f1p, f2p, B, D, H, W, lay, (__nv_bfloat16 *)pyramid, false, nh, s)
+           : vol_dtype == RC_VOL_F16 ? build_tc_t<__half, true>(f1p, f2p, B, D, H, W, lay, (__half *)pyramid, false, nh, s)
+                                     : build_tc_t<float, true>(f1p, f2p, B, D, H, W, lay, (float *)pyramid, false, nh, s);
   if (math != RC_MATH_BF16 && math != RC_MATH_F16) {
     set_error("tensor-core build: math=%d is not a tensor-core mode", math);
     return RC_EINVAL;
   }
   const bool half = math == RC_MATH_F16;
-  return vol_dtype == RC_VOL_BF16  ? build_tc_t<__nv_bfloat16, false>(f1p, f2p, B, D, H, W, lay, (__nv_bfloat16 *)pyramid, half, s)
-         : vol_dtype == RC_VOL_F16 ? build_tc_t<__half, false>(f1p, f2p, B, D, H, W, lay, (__half *)pyramid, half, s)
-                                   : build_tc_t<float, false>(f1p, f2p, B, D, H, W, lay, (float *)pyramid, half, s);
+  return vol_dtype == RC_VOL_BF16  ? build_tc_t<__nv_bfloat16, false>(f1p, f2p, B, D, H, W, lay, (__nv_bfloat16 *)pyramid, half, nh, s)
+         : vol_dtype == RC_VOL_F16 ? build_tc_t<__half, false>(f1p, f2p, B, D, H, W, lay, (__half *)pyramid, half, nh, s)
+                                   : build_tc_t<float, false>(f1p, f2p, B, D, H, W, lay, (float *)pyramid, half, nh, s);
 }
 
 }  // namespace rc

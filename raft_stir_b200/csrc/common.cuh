@@ -149,7 +149,10 @@ int launch_pool_levels(const rc_layout &lay, int vol_dtype, void *pyramid, int f
                        cudaStream_t s);
 // build_tc.cu
 int launch_build_tc(const void *f1p, const void *f2p, int B, int D, int H, int W,
-                    const rc_layout &lay, int vol_dtype, int math, void *pyramid, cudaStream_t s);
+                    const rc_layout &lay, int vol_dtype, int math, int nhwc, void *pyramid, cudaStream_t s);
+// pack.cu: fp32 NCHW -> 16-bit NHWC, both maps, unscaled
+int launch_pack_nhwc16(const float *fmap1, const float *fmap2, int B, int D, int H, int W, int half_operands,
+                       void *f1_nhwc, void *f2_nhwc, cudaStream_t s);
 // lookup.cu
 int launch_lookup_fwd_f16(const void *pyramid, int vol_dtype, const float *coords, const rc_layout &lay, int radius,
                           void *out_f16, cudaStream_t s);

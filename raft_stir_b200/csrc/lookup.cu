@@ -32,6 +32,8 @@
 #include "common.cuh"
 #include <cuda_fp16.h>
 
+#include <atomic>
+
 namespace rc {
 namespace {
 
@@ -68,8 +70,11 @@ struct QueryWin {
 };
 
 // Window origin of a query at a level.  x / 2^l is an exact scaling, identical
-// to the reference's division (core/corr.py:41).  Non-finite or absurd
-// coordinates are treated as "window entirely outside" -> zeros.
+// to the reference's division (core/corr.py:41).  Finite coordinates far outside
+// the map give an all-zero window (zeros padding).  NaN or infinite coordinates
+// give NaN in every sample of the query, as the reference's grid_sample does (a
+// diverging training run must not turn into finite zeros): the window is taken
+// as outside and the fractional offset as NaN, which every lerp propagates.
 template <int R>
 __device__ __forceinline__ QueryWin make_window(float x, float y, int level, bool active) {
   const float inv = __int_as_float((127 - level) << 23);   // 2^-level
@@ -77,10 +82,12 @@ __device__ __forceinline__ QueryWin make_window(float x, float y, int level, boo
   const float fx = floorf(cx), fy = floorf(cy);
   QueryWin w;
   const bool sane = active && fabsf(cx) < 1.0e7f && fabsf(cy) < 1.0e7f;
+  const bool finite = (cx - cx == 0.f) && (cy - cy == 0.f);      // false for NaN and +-Inf
+  const float off = (active && !finite) ? __int_as_float(0x7fc00000) : 0.f;
   w.x0 = sane ? (int)fx - R : -(1 << 24);
   w.y0 = sane ? (int)fy - R : -(1 << 24);
-  w.ax = sane ? cx - fx : 0.f;
-  w.ay = sane ? cy - fy : 0.f;
+  w.ax = sane ? cx - fx : off;
+  w.ay = sane ? cy - fy : off;
   return w;
 }
 
@@ -465,6 +472,20 @@ lookup_bwd_kernel(const VolT *__restrict__ pyr, const float *__restrict__ coords
   }
 }
 
+// Raise a kernel's dynamic shared memory limit to `max_bytes` once per device (`done`: one flag array per kernel
+// instantiation, owned by the caller).  Setting the attribute to the launch's own size on every call would let two
+// host threads with different level counts interleave set and launch.
+static int raise_smem_limit_once(const void *kern, size_t max_bytes, std::atomic<int> (&done)[64]) {
+  int dev = 0;
+  RC_CUDA(cudaGetDevice(&dev));
+  RC_REQUIRE(dev >= 0 && dev < 64, "device index %d out of range", dev);
+  if (!done[dev].load(std::memory_order_acquire)) {
+    RC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)max_bytes));
+    done[dev].store(1, std::memory_order_release);
+  }
+  return RC_OK;
+}
+
 template <typename VolT, int R, typename OutT>
 int lookup_fwd_t(const VolT *pyr, const float *coords, const rc_layout &lay, OutT *out,
                  cudaStream_t s) {
@@ -473,7 +494,8 @@ int lookup_fwd_t(const VolT *pyr, const float *coords, const rc_layout &lay, Out
   const int strips = ceil_div(N, 32);
   const size_t smem = (size_t)lay.num_levels * W_::WIN_BYTES;
   auto kern = lookup_fwd_kernel<VolT, R, OutT>;
-  RC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  static std::atomic<int> limit_set[64];
+  if (int r = raise_smem_limit_once((const void *)kern, (size_t)RC_MAX_LEVELS * W_::WIN_BYTES, limit_set)) return r;
   kern<<<lay.B * strips, 32 * lay.num_levels, smem, s>>>(pyr, coords, out, to_levels(lay), N, strips);
   RC_LAUNCH_CHECK("lookup_fwd_kernel");
   return RC_OK;
@@ -489,7 +511,9 @@ int lookup_bwd_t(const VolT *pyr, const float *coords, const float *grad_out, co
   const size_t per_level = (gpyr ? (size_t)32 * G_::WPQ * 4 : 0) + (gcoords ? (size_t)W_::WIN_BYTES : 0);
   const size_t smem = (size_t)lay.num_levels * per_level;
   auto kern = lookup_bwd_kernel<VolT, R>;
-  RC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  static std::atomic<int> limit_set[64];
+  const size_t max_smem = (size_t)RC_MAX_LEVELS * ((size_t)32 * G_::WPQ * 4 + (size_t)W_::WIN_BYTES);
+  if (int r = raise_smem_limit_once((const void *)kern, max_smem, limit_set)) return r;
   kern<<<lay.B * strips, 32 * lay.num_levels, smem, s>>>(pyr, coords, grad_out, gpyr, gcoords,
                                                          to_levels(lay), to_levels(glay), N, strips);
   RC_LAUNCH_CHECK("lookup_bwd_kernel");

@@ -118,4 +118,24 @@ int launch_pack(const float *fmap1, const float *fmap2, int B, int D, int H, int
   return RC_OK;
 }
 
+// fp32 NCHW -> 16-bit NHWC [B][H][W][D] for both maps (the layout a channels_last 16-bit encoder emits): the same
+// transposing kernel with every row group in plain pixel order and no scale.
+int launch_pack_nhwc16(const float *fmap1, const float *fmap2, int B, int D, int H, int W, int half_operands,
+                       void *f1_nhwc, void *f2_nhwc, cudaStream_t s) {
+  const int N = H * W;
+  const int groups = ceil_div(N, PK_ROWS);
+  dim3 grid(groups, ceil_div(D, PK_D), B);
+  for (int which = 0; which < 2; ++which) {
+    const float *src = which ? fmap2 : fmap1;
+    void *dst = which ? f2_nhwc : f1_nhwc;
+    if (half_operands)
+      pack_features_kernel<__half><<<grid, 256, 0, s>>>(src, nullptr, (__half *)dst, nullptr, D, H, W, groups, 1, 0, 1.f);
+    else
+      pack_features_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>(src, nullptr, (__nv_bfloat16 *)dst, nullptr, D, H, W,
+                                                               groups, 1, 0, 1.f);
+    RC_LAUNCH_CHECK("pack_features_kernel (NHWC)");
+  }
+  return RC_OK;
+}
+
 }  // namespace rc

@@ -268,17 +268,30 @@ def test_lookup_fp16_output_is_the_fp32_output_rounded_once(radius, storage):
         R.CorrBlock(f1, f2, 4, radius, out_dtype=torch.bfloat16)
 
 
-def test_lookup_far_and_nonfinite_coords_are_zero():
-    B, H, W = 1, 16, 24
+def test_lookup_far_coords_are_zero_and_nonfinite_coords_are_nan():
+    """Finite coordinates far outside the map: zeros (grid_sample's zeros padding).  NaN or infinite coordinates: NaN
+    in every sample of that query and nowhere else, as the reference's CorrBlock gives on CPU (probed: NaN, +Inf, -Inf
+    -> NaN; 1e30 -> 0) -- a diverging run must not be masked by finite zeros."""
+    B, D, H, W = 1, 64, 16, 24
     rng = np.random.default_rng(0)
-    blk = R.CorrBlock(t(rng.standard_normal((B, 16, H, W)).astype(np.float32)),
-                      t(rng.standard_normal((B, 16, H, W)).astype(np.float32)), 4, 4)
-    c = torch.full((B, 2, H, W), 3.0e9, device=dev())
-    assert not blk(c).any().item()
-    c = torch.full((B, 2, H, W), float("inf"), device=dev())
-    assert not blk(c).any().item()
-    c = torch.full((B, 2, H, W), -1.0e4, device=dev())
-    assert not blk(c).any().item()
+    f1 = t(rng.standard_normal((B, D, H, W)).astype(np.float32))
+    f2 = t(rng.standard_normal((B, D, H, W)).astype(np.float32))
+    blocks = [R.CorrBlock(f1, f2, 4, 4), R.CorrBlock(f1, f2, 4, 4, storage="fp32", math="fp32"),
+              R.AlternateCorrBlock(f1, f2, 4, 4, math="fp32"), R.AlternateCorrBlock(f1, f2, 4, 4, math="bf16")]
+    for blk in blocks:
+        for far in (3.0e9, -1.0e4, 1.0e30):
+            assert not blk(torch.full((B, 2, H, W), far, device=dev())).any().item()
+        c = R.coords_grid(B, H, W, dev())
+        bad = [(3, 3, 0, float("nan")), (5, 5, 1, float("inf")), (7, 20, 0, -float("inf"))]
+        for y, x, ch, v in bad:
+            c[0, ch, y, x] = v
+        out = blk(c)
+        nan_px = torch.isnan(out).any(dim=1)[0]
+        want = torch.zeros(H, W, dtype=torch.bool, device=dev())
+        for y, x, _, _ in bad:
+            want[y, x] = True
+            assert torch.isnan(out[0, :, y, x]).all(), f"{type(blk).__name__}: not every sample of the query is NaN"
+        assert torch.equal(nan_px, want), f"{type(blk).__name__}: NaN leaked to other queries"
 
 
 # ------------------------------------------------------------------ backward
