@@ -619,8 +619,16 @@ def run_network_extras(R, device):
         ms_ref, (_, up_ref) = timeit(lambda: Hn.raft_forward(nets, im1, im2, 12, Hn.TorchCorrBlock), 3, 5)
         ms_our, (_, up) = timeit(lambda: Hn.raft_forward(nets, im1, im2, 12, R.CorrBlock), 3, 5)
         ms_alt, (_, up_alt) = timeit(lambda: Hn.raft_forward(nets, im1, im2, 12, R.AlternateCorrBlock), 3, 5)
+        try:      # the whole forward as one CUDA graph (raft_stir_b200.GraphedCallable)
+            graphed = R.GraphedCallable(lambda a, b: Hn.raft_forward(nets, a, b, 12, R.CorrBlock), (im1, im2))
+            ms_graph, (_, up_g) = timeit(graphed.replay, 2, 10)
+            graph_epe = torch.sqrt(((up_g - up_ref) ** 2).sum(1)).mean().item()
+            del graphed
+        except Exception as e:
+            ms_graph, graph_epe = None, f"{type(e).__name__}: {str(e)[:200]}"
         out["config1_raft_440x1024_12it"] = {
             "torch_corrblock_ms": ms_ref, "this_library_bf16_ms": ms_our, "this_library_on_the_fly_ms": ms_alt,
+            "this_library_bf16_one_cuda_graph_ms": ms_graph, "mean_epe_delta_px_cuda_graph": graph_epe,
             "pairs_per_s": {"torch_corrblock": 1e3 / ms_ref, "this_library_bf16": 1e3 / ms_our},
             "mean_epe_delta_px": torch.sqrt(((up - up_ref) ** 2).sum(1)).mean().item(),
             "mean_epe_delta_px_on_the_fly": torch.sqrt(((up_alt - up_ref) ** 2).sum(1)).mean().item(),

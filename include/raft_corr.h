@@ -28,7 +28,7 @@ extern "C" {
 #define RC_API
 #endif
 
-#define RC_ABI_VERSION 5
+#define RC_ABI_VERSION 6
 #define RC_MAX_LEVELS 6
 
 /* error codes */
@@ -176,6 +176,26 @@ RC_API int rc_lookup_fwd(const void *pyramid, int vol_dtype, const float *coords
  */
 RC_API int rc_lookup_fwd_f16(const void *pyramid, int vol_dtype, const float *coords, int B, int H, int W,
                       int num_levels, int radius, void *out_f16, rc_stream_t stream);
+
+/*
+ * The lookup fused with the layer that consumes it: the motion encoder's
+ *     cor = F.relu(self.convc1(corr))          convc1 = Conv2d(num_levels*(2r+1)^2, O, kernel 1)
+ * of core/update.py:70-71 (SmallMotionEncoder) and :88-90 (BasicMotionEncoder).  The reference writes the lookup's
+ * samples as fp32 [B, C, H, W], reads them back and convolves in fp32; here the lookup leaves them once, in half
+ * precision, in `workspace`, and a tcgen05 GEMM (fp16 operands, fp32 accumulate, weights resident in shared memory)
+ * applies weights, bias and ReLU: half the intermediate bytes, no fp32 round trip, the contraction on the tensor cores.
+ *   weight_f16 : the layer's weight [O, C] converted once by rc_convc1_pack_weights (rc_convc1_weight_bytes bytes,
+ *                128-byte aligned); bias: fp32 [O]; O a multiple of 16, at most 256
+ *   out        : [B, O, H, W], fp32 (RC_VOL_F32) or fp16 (RC_VOL_F16, for an update block under fp16 autocast)
+ *   workspace  : >= rc_lookup_convc1_workspace_bytes(...) bytes, 128-byte aligned
+ * Inference only (no backward).  Same coordinate conventions as rc_lookup_fwd.
+ */
+RC_API int64_t rc_convc1_weight_bytes(int O, int C);
+RC_API int rc_convc1_pack_weights(const float *weight, int O, int C, void *weight_f16, rc_stream_t stream);
+RC_API int64_t rc_lookup_convc1_workspace_bytes(int B, int H, int W, int num_levels, int radius);
+RC_API int rc_lookup_convc1_fwd(const void *pyramid, int vol_dtype, const float *coords, int B, int H, int W,
+                         int num_levels, int radius, const void *weight_f16, const float *bias, int O, void *out,
+                         int out_dtype, void *workspace, size_t workspace_bytes, rc_stream_t stream);
 
 /*
  * Backward of rc_lookup_fwd: what autograd of F.grid_sample yields at

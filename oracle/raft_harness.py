@@ -91,10 +91,26 @@ class TorchCorrBlock:
 
 
 @torch.no_grad()
+def update_after_convc1(update, net, inp, cor, flow):
+    """BasicUpdateBlock.forward (core/update.py:131-139) with BasicMotionEncoder.forward (:88-95) inlined and its first
+    line, `cor = F.relu(self.convc1(corr))`, already done by the caller: `cor` is that activation.  Every layer is the
+    traced reference submodule; only the wiring between them is restated here (for the fused lookup + convc1 check)."""
+    enc = update.encoder
+    cor = F.relu(enc.convc2(cor))
+    flo = F.relu(enc.convf1(flow))
+    flo = F.relu(enc.convf2(flo))
+    out = F.relu(enc.conv(torch.cat([cor, flo], dim=1)))
+    motion = torch.cat([out, flow], dim=1)
+    net = update.gru(net, torch.cat([inp, motion], dim=1))
+    return net, 0.25 * update.mask(net), update.flow_head(net)
+
+
 def raft_forward(nets, image1, image2, iters=12, corr_cls=TorchCorrBlock, last_only=True, upsample_fn=None,
-                 mixed_precision=False):
+                 mixed_precision=False, fuse_convc1=False):
     """RAFT.forward(test_mode=True) (core/raft.py:86-144) -> (flow_low, flow_up).  mixed_precision wraps the three
-    network calls in fp16 autocast exactly where the reference does (core/raft.py:98-100, :110-114, :127-128)."""
+    network calls in fp16 autocast exactly where the reference does (core/raft.py:98-100, :110-114, :127-128).
+    fuse_convc1: corr_cls's block offers lookup_convc1(coords, weight, bias) (lookup + the motion encoder's first
+    layer in one pass); the rest of the update block runs through update_after_convc1."""
     fnet, cnet, update = nets
     amp = lambda: torch.autocast("cuda", dtype=torch.float16, enabled=mixed_precision)   # noqa: E731
     image1 = (2 * (image1 / 255.0) - 1.0).contiguous()
@@ -114,10 +130,17 @@ def raft_forward(nets, image1, image2, iters=12, corr_cls=TorchCorrBlock, last_o
     coords0 = coords_grid(B, H8, W8, image1.device)
     coords1 = coords0.clone()
     flow_up = None
+    if fuse_convc1:
+        w1, b1 = update.encoder.convc1.weight, update.encoder.convc1.bias
     for it in range(iters):
-        corr = corr_fn(coords1)
-        with amp():
-            net, up_mask, delta = update(net, inp, corr, coords1 - coords0)
+        if fuse_convc1:
+            cor = corr_fn.lookup_convc1(coords1, w1, b1)
+            with amp():
+                net, up_mask, delta = update_after_convc1(update, net, inp, cor, coords1 - coords0)
+        else:
+            corr = corr_fn(coords1)
+            with amp():
+                net, up_mask, delta = update(net, inp, corr, coords1 - coords0)
         coords1 = coords1 + delta
         if not last_only or it == iters - 1:
             flow_up = (upsample_fn or upsample_flow)(coords1 - coords0, up_mask)   # the reference: every iteration

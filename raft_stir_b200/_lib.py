@@ -8,7 +8,7 @@ import os
 RC_MAX_LEVELS = 6
 RC_VOL_F32, RC_VOL_BF16, RC_VOL_F16 = 0, 1, 2
 RC_MATH_F32, RC_MATH_BF16, RC_MATH_TF32, RC_MATH_F16 = 0, 1, 2, 3
-RC_ABI_VERSION = 5
+RC_ABI_VERSION = 6
 RC_STATIC_SCRATCH_BYTES = 16 << 20
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
@@ -39,6 +39,10 @@ SIGNATURES = {
     "rc_pack_features_nhwc16": (_i, [_p, _p, _i, _i, _i, _i, _i, _p, _p, _p]),
     "rc_build_pyramid_nhwc16": (_i, [_p, _p, _i, _i, _i, _i, _i, _i, _i, _p, _p]),
     "rc_lookup_fwd": (_i, [_p, _i, _p, _i, _i, _i, _i, _i, _p, _p]),
+    "rc_convc1_weight_bytes": (_i64, [_i, _i]),
+    "rc_convc1_pack_weights": (_i, [_p, _i, _i, _p, _p]),
+    "rc_lookup_convc1_workspace_bytes": (_i64, [_i, _i, _i, _i, _i]),
+    "rc_lookup_convc1_fwd": (_i, [_p, _i, _p, _i, _i, _i, _i, _i, _p, _p, _i, _p, _i, _p, _sz, _p]),
     "rc_lookup_bwd": (_i, [_p, _i, _p, _p, _i, _i, _i, _i, _i, _p, _p, _p]),
     "rc_build_bwd_workspace_bytes": (_i64, [_i, _i, _i, _i, _i]),
     "rc_build_bwd": (_i, [_p, _p, _p, _i, _i, _i, _i, _i, _i, _p, _p, _p, _sz, _p]),

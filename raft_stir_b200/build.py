@@ -18,7 +18,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "_build")
 LIB = os.path.join(HERE, "libraftcorr.so")
-SOURCES = ["api.cu", "pack.cu", "build_simt.cu", "build_tc.cu", "build_bwd.cu", "lookup.cu", "alt.cu", "alt_tc.cu", "upsample.cu"]
+SOURCES = ["api.cu", "pack.cu", "build_simt.cu", "build_tc.cu", "build_bwd.cu", "lookup.cu", "convc1_tc.cu", "alt.cu", "alt_tc.cu", "upsample.cu"]
 HEADERS = [os.path.join(CSRC, "common.cuh"), os.path.join(CSRC, "tc_ptx.cuh"), os.path.join(HERE, "..", "include", "raft_corr.h")]
 
 NVCC_FLAGS = [

@@ -104,6 +104,84 @@ def pack_features(fmap1: torch.Tensor, fmap2: torch.Tensor, dtype: torch.dtype =
     return o1, o2
 
 
+def pack_convc1_weights(weight: torch.Tensor) -> torch.Tensor:
+    """[O, C(,1,1)] fp32 convolution weight -> the fp16 [O, C rounded up to 8] operand rc_lookup_convc1_fwd reads."""
+    w = _require_cuda_f32(weight.detach().reshape(weight.shape[0], -1), "weight")
+    O, C_ = int(w.shape[0]), int(w.shape[1])
+    L = _lib.lib()
+    nbytes = int(L.rc_convc1_weight_bytes(O, C_))
+    if nbytes <= 0:
+        raise RaftCorrError(f"convc1 weight [{O}, {C_}]: the output channels must be a multiple of 16, at most 256")
+    out = torch.empty(nbytes // 2, dtype=torch.float16, device=w.device)
+    with _guard(w.device):
+        check(L.rc_convc1_pack_weights(w.data_ptr(), O, C_, out.data_ptr(), _stream(w)), "rc_convc1_pack_weights")
+    return out
+
+
+class LazyCorr:
+    """What a CorrBlock(fuse_convc1=True) returns from `corr_fn(coords)`: the block and the coordinates, not yet
+    looked up.  RAFT.forward only passes it on to the update block (core/raft.py:124-128), whose motion encoder
+    applies convc1 first (core/update.py:89): a FusedConvc1 in that place computes lookup + convolution + ReLU in
+    one fused pass.  `materialize()` gives the plain [B, L*(2r+1)^2, H, W] tensor for any other consumer."""
+    __slots__ = ("block", "coords")
+
+    def __init__(self, block, coords):
+        self.block, self.coords = block, coords
+
+    def materialize(self) -> torch.Tensor:
+        return self.block._lookup(self.coords, self.block.out_dtype)
+
+    @property
+    def shape(self):
+        n = 2 * self.block.radius + 1
+        return torch.Size((self.block.B, self.block.num_levels * n * n, self.block.H, self.block.W))
+
+
+class FusedConvc1(torch.nn.Module):
+    """Drop-in for the motion encoder's `convc1` (core/update.py:62, :82).  Given a LazyCorr it returns
+    relu(convc1(lookup)) from the fused kernels (the encoder's own F.relu on top is then the identity); given a
+    tensor it is the wrapped convolution, so training and every other path are unchanged."""
+
+    def __init__(self, conv: torch.nn.Conv2d):
+        super().__init__()
+        if tuple(conv.kernel_size) != (1, 1) or conv.bias is None:
+            raise RaftCorrError("FusedConvc1 wraps a 1x1 convolution with bias")
+        self.conv = conv
+        self._packed = None
+        self._key = None
+
+    @property
+    def weight(self):
+        return self.conv.weight
+
+    @property
+    def bias(self):
+        return self.conv.bias
+
+    def forward(self, corr):
+        if not isinstance(corr, LazyCorr):
+            return self.conv(corr)
+        w = self.conv.weight
+        key = (w.data_ptr(), w._version, w.device)
+        if self._key != key:                      # converted once per weight version (inference: once)
+            self._packed, self._key = pack_convc1_weights(w), key
+        out_dtype = torch.float16 if torch.is_autocast_enabled() and torch.get_autocast_gpu_dtype() is torch.float16 \
+            else torch.float32
+        return corr.block.lookup_convc1(corr.coords, w, self.conv.bias, out_dtype, self._packed)
+
+
+def fuse_motion_encoder(model) -> int:
+    """Wrap `convc1` of every motion encoder inside `model` (a reference RAFT, possibly inside nn.DataParallel) with
+    FusedConvc1; returns how many were wrapped.  Use together with install_into(raft_module, fuse_convc1=True)."""
+    n = 0
+    for mod in model.modules():
+        conv = getattr(mod, "convc1", None)
+        if isinstance(conv, torch.nn.Conv2d) and tuple(conv.kernel_size) == (1, 1):
+            mod.convc1 = FusedConvc1(conv)
+            n += 1
+    return n
+
+
 class _BuildFn(torch.autograd.Function):
     """Autograd node of the volume build.  Its output is a one-element token
     that every lookup takes as an input, so autograd runs this backward once,
@@ -163,15 +241,22 @@ class CorrBlock:
              would cast the fp32 result itself; the lookup then writes half the bytes and the cast pass disappears.
     Defaults can be set with RAFT_CORR_STORAGE / RAFT_CORR_MATH / RAFT_CORR_OUT (fp32|fp16).
 
+    fuse_convc1: in inference the call returns a LazyCorr (block + coordinates) instead of the 324-channel tensor; the
+             motion encoder's first layer, wrapped by `fuse_motion_encoder(model)`, resolves it with ONE fused pass
+             (lookup -> fp16 samples -> tensor-core 1x1 convolution + bias + ReLU, rc_lookup_convc1_fwd).  Anything else
+             that touches the LazyCorr as a tensor gets the ordinary lookup through `.materialize()`.
+
     Features that are already 16-bit (torch.bfloat16 / torch.float16, D % 64 == 0, no gradient wanted) -- what an
     encoder run in channels_last bf16 hands over, or `pack_features` -- are consumed in place: no fp32 round trip, no
     repack, no workspace (rc_build_pyramid_nhwc16); `math` is then the tensors' own type.
     """
 
     def __init__(self, fmap1, fmap2, num_levels: int = 4, radius: int = 4, *,
-                 storage: Optional[str] = None, math: Optional[str] = None, out_dtype: Optional[torch.dtype] = None):
+                 storage: Optional[str] = None, math: Optional[str] = None, out_dtype: Optional[torch.dtype] = None,
+                 fuse_convc1: bool = False):
         self.num_levels = num_levels
         self.radius = radius
+        self.fuse_convc1 = bool(fuse_convc1)
         if out_dtype is None:
             out_dtype = {"fp32": torch.float32, "fp16": torch.float16}.get(os.environ.get("RAFT_CORR_OUT", "fp32"))
         if out_dtype not in (torch.float32, torch.float16):
@@ -265,11 +350,41 @@ class CorrBlock:
                      self.num_levels, self.radius, out.data_ptr(), _stream(coords)), "rc_lookup_fwd")
         return out
 
-    def __call__(self, coords: torch.Tensor) -> torch.Tensor:
+    def __call__(self, coords: torch.Tensor):
         c = self._check_coords(coords)
         if torch.is_grad_enabled() and (self._token is not None or c.requires_grad):
             return _LookupFn.apply(c, self._token, self)      # training: fp32, as the reference
+        if self.fuse_convc1:
+            return LazyCorr(self, c)                          # resolved by the motion encoder's first layer (FusedConvc1)
         return self._lookup(c, self.out_dtype)
+
+    def lookup_convc1(self, coords: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor,
+                      out_dtype: torch.dtype = torch.float32, packed_weight: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """relu(conv1x1(lookup(coords), weight, bias)): the lookup fused with the motion encoder's first layer
+        (core/update.py:70-71, :88-90), [B, O, H, W].  weight: [O, C] or [O, C, 1, 1] fp32, C = num_levels*(2r+1)^2;
+        packed_weight: what pack_convc1_weights(weight) returned (converted here when absent).  Inference only."""
+        c = self._check_coords(coords.detach())
+        L = _lib.lib()
+        n = 2 * self.radius + 1
+        C_ = self.num_levels * n * n
+        O = int(weight.shape[0])
+        if packed_weight is None:
+            packed_weight = pack_convc1_weights(weight)
+        if tuple(weight.shape[:2]) != (O, C_) or bias.numel() != O:
+            raise RaftCorrError(f"weight {tuple(weight.shape)} / bias {tuple(bias.shape)}: expected [{O}, {C_}(,1,1)] and [{O}]")
+        if out_dtype not in (torch.float32, torch.float16):
+            raise RaftCorrError(f"out_dtype={out_dtype!r}: expected torch.float32 or torch.float16")
+        b32 = _require_cuda_f32(bias.detach(), "bias")
+        ws_bytes = int(L.rc_lookup_convc1_workspace_bytes(self.B, self.H, self.W, self.num_levels, self.radius))
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=self.device)
+        out = torch.empty(self.B, O, self.H, self.W, dtype=out_dtype, device=self.device)
+        with _guard(self.device):
+            check(L.rc_lookup_convc1_fwd(self._buf.data_ptr(), self.vol_dtype, c.data_ptr(), self.B, self.H, self.W,
+                                         self.num_levels, self.radius, packed_weight.data_ptr(), b32.data_ptr(), O,
+                                         out.data_ptr(), _lib.RC_VOL_F32 if out_dtype is torch.float32 else _lib.RC_VOL_F16,
+                                         ws.data_ptr(), ws_bytes, _stream(c)), "rc_lookup_convc1_fwd")
+        ws.record_stream(torch.cuda.current_stream(self.device))
+        return out
 
     # --------------------------------------------------------------- backward
     def _lookup_backward(self, coords, grad_out, want_vol: bool, want_coords: bool):
@@ -384,10 +499,16 @@ class AlternateCorrBlock:
         return out
 
 
-def install_into(raft_module, upsampling: bool = True) -> None:
+def install_into(raft_module, upsampling: bool = True, fuse_convc1: bool = False) -> None:
     """Swap the two names `core/raft.py:8` imports, e.g. install_into(sys.modules['raft']); with `upsampling`
-    also rebind the flow upsampling that follows every iteration (core/raft.py:72-83, :133-135)."""
-    raft_module.CorrBlock = CorrBlock
+    also rebind the flow upsampling that follows every iteration (core/raft.py:72-83, :133-135).  fuse_convc1: the
+    blocks RAFT.forward creates hand the update block a LazyCorr (see CorrBlock); call fuse_motion_encoder(model) on
+    the model as well, or the encoder's convolution will not know what to do with it."""
+    if fuse_convc1:
+        import functools
+        raft_module.CorrBlock = functools.partial(CorrBlock, fuse_convc1=True)
+    else:
+        raft_module.CorrBlock = CorrBlock
     raft_module.AlternateCorrBlock = AlternateCorrBlock
     if upsampling:
         from . import upsample as _up

@@ -235,7 +235,48 @@ int rc_lookup_fwd_f16(const void *pyramid, int vol_dtype, const float *coords, i
   rc_layout lay;
   int r = make_layout(B, H, W, num_levels, vol_dtype, &lay);
   if (r) return r;
-  return launch_lookup_fwd_f16(pyramid, vol_dtype, coords, lay, radius, out_f16, (cudaStream_t)stream);
+  return launch_lookup_fwd_f16(pyramid, vol_dtype, coords, lay, radius, out_f16, 0, (cudaStream_t)stream);
+}
+
+int64_t rc_convc1_weight_bytes(int O, int C) {
+  if (O < 16 || O > 256 || O % 16 != 0 || C < 1) return RC_EINVAL;
+  return (int64_t)O * convc1_cp(C) * 2;
+}
+
+int rc_convc1_pack_weights(const float *weight, int O, int C, void *weight_f16, rc_stream_t stream) {
+  RC_REQUIRE(weight && weight_f16, "rc_convc1_pack_weights: NULL pointer");
+  RC_REQUIRE(O >= 16 && O <= 256 && O % 16 == 0 && C >= 1, "rc_convc1_pack_weights: O=%d must be a multiple of 16 in 16..256, C=%d >= 1", O, C);
+  return launch_convc1_pack_weights(weight, O, C, weight_f16, (cudaStream_t)stream);
+}
+
+int64_t rc_lookup_convc1_workspace_bytes(int B, int H, int W, int num_levels, int radius) {
+  if (B < 1 || H < 1 || W < 1 || num_levels < 1 || num_levels > RC_MAX_LEVELS || radius < 1 || radius > 4) return RC_EINVAL;
+  const int64_t C = (int64_t)num_levels * (2 * radius + 1) * (2 * radius + 1);
+  return round_up64((int64_t)B * C * convc1_npad(H * W) * 2, 256);
+}
+
+int rc_lookup_convc1_fwd(const void *pyramid, int vol_dtype, const float *coords, int B, int H, int W, int num_levels,
+                         int radius, const void *weight_f16, const float *bias, int O, void *out, int out_dtype,
+                         void *workspace, size_t workspace_bytes, rc_stream_t stream) {
+  RC_REQUIRE(pyramid && coords && weight_f16 && bias && out, "rc_lookup_convc1_fwd: NULL pointer");
+  RC_REQUIRE(radius >= 1 && radius <= 4, "radius %d unsupported (1..4)", radius);
+  RC_REQUIRE(O >= 16 && O <= 256 && O % 16 == 0, "rc_lookup_convc1_fwd: O=%d must be a multiple of 16 in 16..256", O);
+  RC_REQUIRE(out_dtype == RC_VOL_F32 || out_dtype == RC_VOL_F16, "rc_lookup_convc1_fwd: out_dtype %d (RC_VOL_F32 or RC_VOL_F16)", out_dtype);
+  rc_layout lay;
+  int r = make_layout(B, H, W, num_levels, vol_dtype, &lay);
+  if (r) return r;
+  const int64_t need = rc_lookup_convc1_workspace_bytes(B, H, W, num_levels, radius);
+  if (workspace == nullptr || (int64_t)workspace_bytes < need) {
+    set_error("rc_lookup_convc1_fwd: workspace of %zu bytes, need %lld", workspace_bytes, (long long)need);
+    return RC_ESIZE;
+  }
+  RC_REQUIRE(((uintptr_t)workspace & 127) == 0 && ((uintptr_t)weight_f16 & 127) == 0,
+             "rc_lookup_convc1_fwd: workspace and weights must be 128-byte aligned");
+  const int N = H * W, C = num_levels * (2 * radius + 1) * (2 * radius + 1);
+  cudaStream_t s = (cudaStream_t)stream;
+  r = launch_lookup_fwd_f16(pyramid, vol_dtype, coords, lay, radius, workspace, convc1_npad(N), s);
+  if (r) return r;
+  return launch_convc1(workspace, weight_f16, bias, B, N, C, O, out, out_dtype == RC_VOL_F16, s);
 }
 
 int rc_lookup_bwd(const void *pyramid, int vol_dtype, const float *coords, const float *grad_out, int B,

@@ -155,7 +155,13 @@ int launch_pack_nhwc16(const float *fmap1, const float *fmap2, int B, int D, int
                        void *f1_nhwc, void *f2_nhwc, cudaStream_t s);
 // lookup.cu
 int launch_lookup_fwd_f16(const void *pyramid, int vol_dtype, const float *coords, const rc_layout &lay, int radius,
-                          void *out_f16, cudaStream_t s);
+                          void *out_f16, int out_pitch, cudaStream_t s);
+// convc1_tc.cu
+int convc1_cp(int C);
+int convc1_npad(int N);
+int launch_convc1_pack_weights(const float *w, int O, int C, void *w16, cudaStream_t s);
+int launch_convc1(const void *samples, const void *w16, const float *bias, int B, int N, int C, int O, void *out,
+                  int out_f16, cudaStream_t s);
 int launch_lookup_fwd(const void *pyramid, int vol_dtype, const float *coords, const rc_layout &lay,
                       int H, int W, int radius, float *out, cudaStream_t s);
 int launch_lookup_bwd(const void *pyramid, int vol_dtype, const float *coords, const float *grad_out,

@@ -242,7 +242,7 @@ __device__ __forceinline__ __half to_out<__half>(float v) { return __float2half_
 template <typename VolT, int R, typename OutT>
 __global__ void __launch_bounds__(32 * RC_MAX_LEVELS)
 lookup_fwd_kernel(const VolT *__restrict__ pyr, const float *__restrict__ coords,
-                  OutT *__restrict__ out, Levels lv, int N, int strips_per_pair) {
+                  OutT *__restrict__ out, Levels lv, int N, int strips_per_pair, int out_pitch) {
   using W_ = Win<VolT, R>;
   extern __shared__ __align__(16) uint32_t smem_u[];
   const int lane = threadIdx.x & 31;
@@ -273,7 +273,8 @@ lookup_fwd_kernel(const VolT *__restrict__ pyr, const float *__restrict__ coords
   if (!active) return;
   const int o = w.x0 & (W_::EPV - 1);
   const int C = lv.num_levels * W_::NW * W_::NW;
-  OutT *op = out + ((size_t)b * C + (size_t)l * W_::NW * W_::NW) * N + q;
+  // out_pitch: elements between consecutive channel planes (N, or N rounded up when a TMA reader needs 16-byte pitches)
+  OutT *op = out + ((size_t)b * C + (size_t)l * W_::NW * W_::NW) * out_pitch + q;
   float hprev[W_::NW];
 #pragma unroll
   for (int j = 0; j < W_::T; ++j) {
@@ -284,7 +285,7 @@ lookup_fwd_kernel(const VolT *__restrict__ pyr, const float *__restrict__ coords
     if (j > 0) {
 #pragma unroll
       for (int i = 0; i < W_::NW; ++i)
-        op[(size_t)(i * W_::NW + (j - 1)) * N] = to_out<OutT>(fmaf(w.ay, h[i] - hprev[i], hprev[i]));
+        op[(size_t)(i * W_::NW + (j - 1)) * out_pitch] = to_out<OutT>(fmaf(w.ay, h[i] - hprev[i], hprev[i]));
     }
 #pragma unroll
     for (int i = 0; i < W_::NW; ++i) hprev[i] = h[i];
@@ -487,7 +488,7 @@ static int raise_smem_limit_once(const void *kern, size_t max_bytes, std::atomic
 }
 
 template <typename VolT, int R, typename OutT>
-int lookup_fwd_t(const VolT *pyr, const float *coords, const rc_layout &lay, OutT *out,
+int lookup_fwd_t(const VolT *pyr, const float *coords, const rc_layout &lay, OutT *out, int out_pitch,
                  cudaStream_t s) {
   using W_ = Win<VolT, R>;
   const int N = lay.N;
@@ -496,7 +497,8 @@ int lookup_fwd_t(const VolT *pyr, const float *coords, const rc_layout &lay, Out
   auto kern = lookup_fwd_kernel<VolT, R, OutT>;
   static std::atomic<int> limit_set[64];
   if (int r = raise_smem_limit_once((const void *)kern, (size_t)RC_MAX_LEVELS * W_::WIN_BYTES, limit_set)) return r;
-  kern<<<lay.B * strips, 32 * lay.num_levels, smem, s>>>(pyr, coords, out, to_levels(lay), N, strips);
+  kern<<<lay.B * strips, 32 * lay.num_levels, smem, s>>>(pyr, coords, out, to_levels(lay), N, strips,
+                                                         out_pitch > 0 ? out_pitch : N);
   RC_LAUNCH_CHECK("lookup_fwd_kernel");
   return RC_OK;
 }
@@ -544,23 +546,23 @@ int launch_lookup_fwd(const void *pyramid, int vol_dtype, const float *coords, c
                       int H, int W, int radius, float *out, cudaStream_t s) {
   (void)H; (void)W;
   if (vol_dtype == RC_VOL_BF16) {
-    RC_DISPATCH_R2(lookup_fwd_t, __nv_bfloat16, float, (const __nv_bfloat16 *)pyramid, coords, lay, out, s)
+    RC_DISPATCH_R2(lookup_fwd_t, __nv_bfloat16, float, (const __nv_bfloat16 *)pyramid, coords, lay, out, 0, s)
   } else if (vol_dtype == RC_VOL_F16) {
-    RC_DISPATCH_R2(lookup_fwd_t, __half, float, (const __half *)pyramid, coords, lay, out, s)
+    RC_DISPATCH_R2(lookup_fwd_t, __half, float, (const __half *)pyramid, coords, lay, out, 0, s)
   } else {
-    RC_DISPATCH_R2(lookup_fwd_t, float, float, (const float *)pyramid, coords, lay, out, s)
+    RC_DISPATCH_R2(lookup_fwd_t, float, float, (const float *)pyramid, coords, lay, out, 0, s)
   }
 }
 
 int launch_lookup_fwd_f16(const void *pyramid, int vol_dtype, const float *coords, const rc_layout &lay, int radius,
-                          void *out_f16, cudaStream_t s) {
+                          void *out_f16, int out_pitch, cudaStream_t s) {
   __half *out = (__half *)out_f16;
   if (vol_dtype == RC_VOL_BF16) {
-    RC_DISPATCH_R2(lookup_fwd_t, __nv_bfloat16, __half, (const __nv_bfloat16 *)pyramid, coords, lay, out, s)
+    RC_DISPATCH_R2(lookup_fwd_t, __nv_bfloat16, __half, (const __nv_bfloat16 *)pyramid, coords, lay, out, out_pitch, s)
   } else if (vol_dtype == RC_VOL_F16) {
-    RC_DISPATCH_R2(lookup_fwd_t, __half, __half, (const __half *)pyramid, coords, lay, out, s)
+    RC_DISPATCH_R2(lookup_fwd_t, __half, __half, (const __half *)pyramid, coords, lay, out, out_pitch, s)
   } else {
-    RC_DISPATCH_R2(lookup_fwd_t, float, __half, (const float *)pyramid, coords, lay, out, s)
+    RC_DISPATCH_R2(lookup_fwd_t, float, __half, (const float *)pyramid, coords, lay, out, out_pitch, s)
   }
 }
 

@@ -183,3 +183,27 @@ def test_mixed_precision_with_fp16_lookup_and_fp16_mask(reference_run):
                              upsample_fn=R.upsample_flow, mixed_precision=True)
     assert _epe(got, ref16) <= 0.01 and _epe(got, up) <= 0.01, (_epe(got, ref16), _epe(got, up))
 
+
+
+def test_whole_forward_as_one_cuda_graph(reference_run):
+    """the reference's 12-iteration loop (core/raft.py:122-139) with this library's block and
+    upsampling, captured once by raft_stir_b200.GraphedCallable and replayed on NEW images: same flow as the eager run
+    on those images (bit-identical kernels, same order) and within the 0.01 px budget of the reference."""
+    nets, im1, im2, low, up = reference_run
+
+    def fwd(a, b):
+        return Hn.raft_forward(nets, a, b, iters=12, corr_cls=R.CorrBlock, upsample_fn=R.upsample_flow)
+
+    g = torch.Generator(device="cpu").manual_seed(77)
+    other1 = (torch.rand(im1.shape, generator=g) * 255).to(im1.device)
+    other2 = (torch.rand(im2.shape, generator=g) * 255).to(im1.device)
+    graphed = R.GraphedCallable(fwd, (other1, other2))          # captured on other images ...
+    _, got = graphed(im1, im2)                                  # ... replayed on the fixture's
+    _, eager = fwd(im1, im2)
+    assert (got - eager).abs().max().item() <= 1e-3      # same kernels in the same order (cuDNN may pick another algorithm)
+    assert _epe(got, up) <= 0.01
+    _, again = graphed(other1, other2)
+    _, eager2 = fwd(other1, other2)
+    assert (again - eager2).abs().max().item() <= 1e-3
+    with pytest.raises(RuntimeError):
+        graphed(im1[:, :, :-8], im2[:, :, :-8])
