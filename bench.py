@@ -579,6 +579,28 @@ def run_extras(R, device, args, pk):
             out["upsample_flow_frac_hbm"] = out["upsample_flow_GB/s"] / pk["hbm_gbs"]
             out["upsample_flow_note"] = f"{Bu} maps of {H}x{W}: 2 304 B mask + 8 B flow in, 512 B out per coarse pixel"
             del fl, mk
+        # lookup -> convc1 -> ReLU (core/update.py:88-90), fused against composed, same batch
+        with torch.no_grad():
+            import torch.nn.functional as F
+            f1b = torch.randn(args.batch, D, H, W, device=device)
+            f2b = torch.randn(args.batch, D, H, W, device=device)
+            cb = R.coords_grid(args.batch, H, W, device) + 5 * torch.randn(args.batch, 2, H, W, device=device)
+            blk = R.CorrBlock(f1b, f2b, LEVELS, RADIUS, storage=args.storage, math=args.math)
+            del f1b, f2b
+            nch = LEVELS * (2 * RADIUS + 1) ** 2
+            wc = torch.randn(256, nch, 1, 1, device=device) / nch ** 0.5
+            bc = 0.1 * torch.randn(256, device=device)
+            wp = R.pack_convc1_weights(wc)
+            out["lookup_convc1_fused_ms"] = timeit(lambda: blk.lookup_convc1(cb, wc, bc, packed_weight=wp), 20)
+            out["lookup_then_cudnn_convc1_relu_ms"] = timeit(lambda: F.relu(F.conv2d(blk(cb), wc, bc)), 10)
+            prev = torch.backends.cudnn.allow_tf32
+            torch.backends.cudnn.allow_tf32 = False
+            out["lookup_then_cudnn_convc1_relu_fp32_ms"] = timeit(lambda: F.relu(F.conv2d(blk(cb), wc, bc)), 5)
+            torch.backends.cudnn.allow_tf32 = prev
+            out["lookup_convc1_note"] = (f"{args.batch} pairs; fused = rc_lookup_convc1_fwd (fp16 samples, tcgen05 1x1 conv + bias + "
+                                         "ReLU, fp32 out); composed = this library's fp32-out lookup + torch conv2d + relu "
+                                         "(cuDNN with its default TF32 setting, and with TF32 off)")
+            del blk, cb
     except Exception as e:  # extras must never sink the headline
         out["error"] = f"{type(e).__name__}: {e}"
     try:
