@@ -20,6 +20,12 @@ WANT = [
     ("dram__bytes_write.sum", "DRAM write"),
     ("dram__bytes.sum.per_second", "DRAM throughput"),
     ("dram__throughput.avg.pct_of_peak_sustained_elapsed", "DRAM % of peak"),
+    ("dram__bytes_write.sum.per_second", "DRAM write throughput"),
+    ("lts__throughput.avg.pct_of_peak_sustained_elapsed", "L2 % of peak"),
+    ("l1tex__m_l1tex2xbar_req_cycles_active.avg.pct_of_peak_sustained_elapsed", "SM->L2 request port busy %"),
+    ("l1tex__m_l1tex2xbar_write_bytes.sum", "SM->L2 write bytes"),
+    ("l1tex__m_xbar2l1tex_read_bytes.sum", "L2->SM read bytes"),
+    ("sm__cycles_elapsed.avg", "SM cycles elapsed"),
     ("l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum", "L1 global-load sectors"),
     ("lts__t_sectors_srcunit_tex_op_read.sum", "L2 read sectors from SMs"),
     ("lts__t_sectors_srcunit_tex_op_read_lookup_miss.sum", "  of which missed"),
