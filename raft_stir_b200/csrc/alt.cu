@@ -60,8 +60,9 @@ alt_fwd_kernel(const float *__restrict__ fmap1, const float *__restrict__ fmap2,
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int b = blockIdx.z, mid = blockIdx.y;
   const int q0 = blockIdx.x * ALT_Q;
-  const int H2 = lv.H2[mid], W2 = lv.W2[mid];
-  const float *f2 = fmap2 + lv.off[mid] + (size_t)b * H2 * W2 * C;
+  const int li = PLANAR ? mid : 0;       // one-level calls (any number of coordinate sets) share entry 0
+  const int H2 = lv.H2[li], W2 = lv.W2[li];
+  const float *f2 = fmap2 + lv.off[li] + (size_t)b * H2 * W2 * C;
 
   for (int qi = warp; qi < ALT_Q; qi += ALT_WARPS) {
     const int q = q0 + qi;
@@ -300,10 +301,8 @@ int alt_bwd_t(const float *f1, const float *f2, const float *coords, const float
 int launch_alt_fwd(const float *fmap1, const float *fmap2, const float *coords, int B, int H1, int W1,
                    int H2, int W2, int C, int Nc, int radius, float *corr, cudaStream_t s) {
   AltLevels lv{};
-  lv.count = Nc;
-  for (int n = 0; n < Nc; ++n) {
-    lv.H2[n] = H2; lv.W2[n] = W2; lv.off[n] = 0; lv.cscale[n] = 1.f;
-  }
+  lv.count = Nc;                          // coordinate sets: grid.y, no per-set table (all sets sample the same fmap2)
+  lv.H2[0] = H2; lv.W2[0] = W2; lv.off[0] = 0; lv.cscale[0] = 1.f;
   RC_ALT_SWITCH((alt_fwd_t<R_, false>(fmap1, fmap2, coords, corr, lv, B, H1 * W1, C, 1.0f, s)))
 }
 

@@ -323,8 +323,9 @@ int rc_alt_fwd(const float *fmap1, const float *fmap2, const float *coords, int 
   RC_REQUIRE(B >= 1 && H1 >= 1 && W1 >= 1 && H2 >= 1 && W2 >= 1 && Nc >= 1, "rc_alt_fwd: bad sizes");
   RC_REQUIRE(C >= 4 && C % 4 == 0 && C <= 512, "rc_alt_fwd: C=%d must be a multiple of 4, at most 512", C);
   RC_REQUIRE(radius >= 1 && radius <= 4, "radius %d unsupported (1..4)", radius);
-  RC_REQUIRE(Nc <= RC_MAX_LEVELS, "rc_alt_fwd: at most %d coordinate sets per call (got %d)",
-             RC_MAX_LEVELS, Nc);
+  RC_REQUIRE(Nc <= 65535, "rc_alt_fwd: at most 65535 coordinate sets per call (got %d)", Nc);
+  RC_REQUIRE((((uintptr_t)fmap1 | (uintptr_t)fmap2) & 15) == 0 && ((uintptr_t)coords & 7) == 0,
+             "rc_alt_fwd: feature maps must be 16-byte aligned, coords 8-byte aligned");
   return launch_alt_fwd(fmap1, fmap2, coords, B, H1, W1, H2, W2, C, Nc, radius, corr, (cudaStream_t)stream);
 }
 
@@ -335,6 +336,9 @@ int rc_alt_bwd(const float *fmap1, const float *fmap2, const float *coords, cons
   RC_REQUIRE(B >= 1 && H1 >= 1 && W1 >= 1 && H2 >= 1 && W2 >= 1 && Nc >= 1, "rc_alt_bwd: bad sizes");
   RC_REQUIRE(C >= 4 && C % 4 == 0 && C <= 512, "rc_alt_bwd: C=%d must be a multiple of 4, at most 512", C);
   RC_REQUIRE(radius >= 1 && radius <= 4, "radius %d unsupported (1..4)", radius);
+  RC_REQUIRE((((uintptr_t)fmap1 | (uintptr_t)fmap2 | (uintptr_t)fmap1_grad | (uintptr_t)fmap2_grad) & 15) == 0 &&
+                 ((uintptr_t)coords & 7) == 0,
+             "rc_alt_bwd: feature maps and their gradients must be 16-byte aligned, coords 8-byte aligned");
   cudaStream_t s = (cudaStream_t)stream;
   RC_CUDA(cudaMemsetAsync(fmap2_grad, 0, (size_t)B * H2 * W2 * C * sizeof(float), s));
   if (coords_grad) RC_CUDA(cudaMemsetAsync(coords_grad, 0, (size_t)B * Nc * H1 * W1 * 2 * sizeof(float), s));
@@ -368,6 +372,7 @@ int rc_alt_lookup_fwd(const float *fmap1_nhwc, const float *fmap2_pyr, const flo
   RC_REQUIRE(radius >= 1 && radius <= 4, "radius %d unsupported (1..4)", radius);
   int64_t off[RC_MAX_LEVELS];
   RC_REQUIRE(rc_alt_feature_pyramid_elems(B, D, H, W, num_levels, off) > 0, "rc_alt_lookup_fwd: bad sizes");
+  RC_REQUIRE((((uintptr_t)fmap1_nhwc | (uintptr_t)fmap2_pyr) & 15) == 0, "rc_alt_lookup_fwd: feature buffers must be 16-byte aligned");
   RC_REQUIRE((H >> (num_levels - 1)) >= 1 && (W >> (num_levels - 1)) >= 1, "map too small for %d levels", num_levels);
   return launch_alt_lookup_fwd(fmap1_nhwc, fmap2_pyr, coords, B, D, H, W, num_levels, radius, off, out,
                                (cudaStream_t)stream);

@@ -94,6 +94,11 @@ __device__ __forceinline__ void tma_load_3d_plain(uint32_t dst, const CUtensorMa
       ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
       : "memory");
 }
+// ask L2 to fetch a box ahead of the TMA load that will need it (no shared-memory slot, no barrier)
+__device__ __forceinline__ void tma_prefetch_3d(const CUtensorMap *map, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.prefetch.tensor.3d.L2.global [%0, {%1, %2, %3}];" ::"l"(map), "r"(c0), "r"(c1), "r"(c2)
+               : "memory");
+}
 __device__ __forceinline__ void stg16_hint(void *dst, const uint4 &v, uint64_t policy) {
   asm volatile("st.global.L2::cache_hint.v4.b32 [%0], {%1, %2, %3, %4}, %5;" ::"l"(dst), "r"(v.x), "r"(v.y), "r"(v.z),
                "r"(v.w), "l"(policy)

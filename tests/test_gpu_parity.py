@@ -382,6 +382,24 @@ def test_alt_cuda_corr_forward_backward_contract():
     assert tuple(gc.shape) == coords.shape and not gc.any().item()   # zeros, as in the reference
 
 
+def test_alt_cuda_corr_many_coordinate_sets():
+    """The reference's alt_cuda_corr.forward takes any number N of coordinate sets (coords [B,N,H,W,2],
+    correlation.cpp:23-33); round 1 stopped at 6."""
+    rng = np.random.default_rng(5)
+    B, H1, W1, H2, W2, Cc, r, Nc = 1, 6, 9, 7, 8, 16, 2, 9
+    f1 = rng.standard_normal((B, H1, W1, Cc)).astype(np.float32)
+    f2 = rng.standard_normal((B, H2, W2, Cc)).astype(np.float32)
+    coords = rng.uniform(-2, 9, (B, Nc, H1, W1, 2)).astype(np.float32)
+    (corr,) = R.alt_cuda_corr.forward(t(f1), t(f2), t(coords), r)
+    assert tuple(corr.shape) == (B, Nc, 25, H1, W1)
+    rel_close(corr.cpu().numpy(), O.alt_forward(f1, f2, coords, r), 1e-4, "alt_cuda_corr.forward, 9 coordinate sets")
+    g = rng.standard_normal(tuple(corr.shape)).astype(np.float32)
+    g1, g2, _ = R.alt_cuda_corr.backward(t(f1), t(f2), t(coords), t(g), r)
+    o1, o2, _ = O.alt_backward(f1, f2, coords, g, r)
+    rel_close(g1.cpu().numpy(), o1, 1e-4, "fmap1_grad, 9 coordinate sets")
+    rel_close(g2.cpu().numpy(), o2, 1e-4, "fmap2_grad, 9 coordinate sets")
+
+
 def test_alternate_equals_default_at_sintel_shape():
     rng = np.random.default_rng(2)
     B, D, H, W = 1, 256, 55, 128
