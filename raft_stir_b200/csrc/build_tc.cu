@@ -188,6 +188,16 @@ __device__ __forceinline__ void flush64(uint32_t ld_base, char *g, long long str
   }
 }
 
+__device__ __forceinline__ void named_bar_arrive(uint32_t id, uint32_t count) {
+  asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory");
+}
+// one full 32-byte sector per lane
+__device__ __forceinline__ void stg32_hint(void *dst, const uint4 &a, const uint4 &b, uint64_t policy) {
+  asm volatile("st.global.L2::cache_hint.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8}, %9;" ::"l"(dst), "r"(a.x), "r"(a.y),
+               "r"(a.z), "r"(a.w), "r"(b.x), "r"(b.y), "r"(b.z), "r"(b.w), "l"(policy)
+               : "memory");
+}
+
 // ---------------------------------------------------------------- the kernel
 // TF32 = false: bf16 operands (kind::f16), the query operand stationary in shared memory.
 // TF32 = true:  fp32 operands read as tf32 (kind::tf32, 32 channels per 128-byte k-block).  Twice the operand bytes
@@ -340,6 +350,7 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
     uint32_t i = 0;
     while (walk.next(p, b, m, n, by, bx)) {
       const uint32_t acc = i & 1, t_par = (i >> 1) & 1;
+      const bool first_tile = i == 0;
       ++i;
       const int x0 = bx * TB_W, y0 = by * TB_H;
       const int xg = x0 + group * GW;                  // first map column of this group's sub-block
@@ -374,6 +385,7 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
       if (lane == 0) mbar_arrive(bar_t_empty + 8 * acc);
 
       float p1prev[8], p2prev[4];
+      uint32_t l2w[4] = {0u, 0u, 0u, 0u}, l3w = 0u;     // 2-byte storage: this thread's level-2 rows and level-3 cells, packed
 #pragma unroll
       for (int rp = 0; rp < 4; ++rp) {
         float v0[GW], v1[GW], p1[8];
@@ -428,9 +440,13 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
           if (L > 2 && lane < nq && (y0 >> 4) < p.tiles_y[2] && x2 / S::TW < p.tiles_x[2]) {
             char *g2 = (char *)p.lvl[2] + ((long long)(y0 >> 4) * p.tiles_x[2] + x2 / S::TW) * 64 +
                        (slab_q0 + lane) * p.slab[2] * ES + (((y0 >> 2) & 3) + (rp >> 1)) * 16 + (x2 % S::TW) * ES;
-            if (ES == 2) stg8_hint(g2, pack2<VolT>(p2[0], p2[1]), pack2<VolT>(p2[2], p2[3]), pol_out);
-            else stg16_hint(g2, make_uint4(__float_as_uint(p2[0]), __float_as_uint(p2[1]), __float_as_uint(p2[2]),
-                                           __float_as_uint(p2[3])), pol_out);
+            if (ES == 4)
+              stg16_hint(g2, make_uint4(__float_as_uint(p2[0]), __float_as_uint(p2[1]), __float_as_uint(p2[2]),
+                                        __float_as_uint(p2[3])), pol_out);
+          }
+          if (ES == 2) {          // stored after the tile, merged with the other group's half (see below)
+            l2w[(rp >> 1) * 2] = pack2<VolT>(p2[0], p2[1]);
+            l2w[(rp >> 1) * 2 + 1] = pack2<VolT>(p2[2], p2[3]);
           }
           if (rp == 3) {
             // ---- level 3: 2 cells
@@ -444,15 +460,9 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
             if (L > 3 && lane < nq && (y0 >> 5) < p.tiles_y[3] && x3 / S::TW < p.tiles_x[3]) {
               char *g3 = (char *)p.lvl[3] + ((long long)(y0 >> 5) * p.tiles_x[3] + x3 / S::TW) * 64 +
                          (slab_q0 + lane) * p.slab[3] * ES + ((y0 >> 3) & 3) * 16 + (x3 % S::TW) * ES;
-              if (ES == 2) {
-                stg4_hint(g3, pack2<VolT>(p3[0], p3[1]), pol_out);
-                // a bf16 tile row holds the cells of two blocks; with no block to the right, its
-                // cells 4..7 are padding columns and must read as zero
-                if (group == 1 && !(bx & 1) && bx + 1 >= p.nbx) stg8_hint(g3 + 4, 0u, 0u, pol_out);
-              } else {
-                stg8_hint(g3, __float_as_uint(p3[0]), __float_as_uint(p3[1]), pol_out);
-              }
+              if (ES == 4) stg8_hint(g3, __float_as_uint(p3[0]), __float_as_uint(p3[1]), pol_out);
             }
+            if (ES == 2) l3w = pack2<VolT>(p3[0], p3[1]);
           } else {
 #pragma unroll
             for (int k = 0; k < 4; ++k) p2prev[k] = p2[k];
@@ -493,6 +503,42 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
           }
         }
         __syncwarp();
+      }
+
+      // ---- levels 2 and 3 with 2-byte storage.  A block's level-2 cells are ONE 32-byte sector per query (2 rows of
+      // 8 cells), its level-3 cells 8 bytes; each column group holds half of either.  Written separately they are
+      // four 8-byte and two 4-byte scattered stores per query, each occupying a whole sector on the way to L2 (a quarter
+      // more write traffic than the kernel has output).  Group 1 hands its halves to group 0 through the unused half
+      // of its level-1 buffer ("full" = named barrier 1 + quarter, "empty" = 5 + quarter, 64 threads each: the
+      // arriving warp and the waiting one); group 0 stores whole sectors.
+      if (ES == 2 && L > 2) {
+        const uint32_t xq = sStage + (((warp - EPI_WARP0) & 3) + 4) * STAGE_BYTES_PER_WARP + STEP_BYTES + 2048 + lane * 32;   // in the group-1 warp's buffer
+        if (group == 1) {
+          if (!first_tile) named_bar_sync(5 + quarter, 64);
+          sts16(xq, l2w[0], l2w[1], l2w[2], l2w[3]);
+          asm volatile("st.shared.b32 [%0], %1;" ::"r"(xq + 16), "r"(l3w) : "memory");
+          named_bar_arrive(1 + quarter, 64);
+        } else {
+          named_bar_sync(1 + quarter, 64);
+          const uint4 o = lds16(xq);
+          uint32_t o3;
+          asm volatile("ld.shared.b32 %0, [%1];" : "=r"(o3) : "r"(xq + 16) : "memory");
+          named_bar_arrive(5 + quarter, 64);
+          const int x2 = x0 >> 2, x3 = x0 >> 3;
+          if (lane < nq && (y0 >> 4) < p.tiles_y[2] && x2 / S::TW < p.tiles_x[2]) {
+            char *g2 = (char *)p.lvl[2] + ((long long)(y0 >> 4) * p.tiles_x[2] + x2 / S::TW) * 64 +
+                       (slab_q0 + lane) * p.slab[2] * ES + ((y0 >> 2) & 3) * 16;
+            stg32_hint(g2, make_uint4(l2w[0], l2w[1], o.x, o.y), make_uint4(l2w[2], l2w[3], o.z, o.w), pol_out);
+          }
+          if (L > 3 && lane < nq && (y0 >> 5) < p.tiles_y[3] && x3 / S::TW < p.tiles_x[3]) {
+            char *g3 = (char *)p.lvl[3] + ((long long)(y0 >> 5) * p.tiles_x[3] + x3 / S::TW) * 64 +
+                       (slab_q0 + lane) * p.slab[3] * ES + ((y0 >> 3) & 3) * 16 + (x3 % S::TW) * ES;
+            // a tile row holds the level-3 cells of two blocks; with no block to the right, its cells 4..7 are
+            // padding columns and must read as zero
+            if (!(bx & 1) && bx + 1 >= p.nbx) stg16_hint(g3, make_uint4(l3w, o3, 0u, 0u), pol_out);
+            else stg8_hint(g3, l3w, o3, pol_out);
+          }
+        }
       }
     }
   }
