@@ -116,17 +116,19 @@ constexpr uint32_t IDESC_TF32 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)
 // tile's targets.  Level 0 leaves in STEPS of 128 bytes per query (bf16: 4 block
 // rows = 2 tiles, contiguous; fp32: 2 block rows = half of 4 tiles, 4 pieces of
 // 32 bytes): the thread parks its 16-byte units in a per-warp buffer, then the
-// warp reads the buffer back query by query and issues coalesced 16-byte stores
-// (8 lanes cover one query's 128 bytes).  The level-1 cells of the sub-block
-// (64 / 128 bytes per query) take the same route once per tile.  Levels 2 and 3
-// (20 / 40 bytes per query and tile) are stored by the owning thread directly.
+// warp reads the buffer back query by query and issues coalesced 32-byte stores
+// (st.global.v8: 4 lanes cover one query's 128 bytes, every lane a full sector).
+// The level-1 cells of the sub-block (64 / 128 bytes per query) take the same
+// route once per tile.  Levels 2 and 3: with fp32 storage the owning thread
+// stores its 16 / 8 bytes directly; with 2-byte storage a thread's share is only
+// 8 / 4 bytes, so the two column groups merge theirs through shared memory and
+// one of them stores whole sectors (end of the epilogue loop).
 template <typename VolT>
 struct Stg;
 struct Stg16 {                            // 2-byte elements (bf16, fp16)
   static constexpr int TW = 8;            // tile width, elements
   static constexpr int L0_GT = 2;         // level-0 tiles per group and row of tiles
   static constexpr int L1_GT = 1;         // level-1 tiles per group
-  static constexpr int STEPS = 2;         // level-0 steps per tile
 };
 template <>
 struct Stg<__nv_bfloat16> : Stg16 {};
@@ -137,7 +139,6 @@ struct Stg<float> {
   static constexpr int TW = 4;
   static constexpr int L0_GT = 4;
   static constexpr int L1_GT = 2;
-  static constexpr int STEPS = 4;
 };
 constexpr int STEP_BYTES = 32 * 128;      // per-warp level-0 step buffer
 constexpr int L1BUF_BYTES = 32 * 128;     // per-warp level-1 buffer (bf16 uses half)
@@ -162,32 +163,9 @@ __device__ __forceinline__ void put_unit(uint32_t addr, const float *v) {
 // Buffers with 128-byte query rows: unit u of query q sits at q*128 + ((u ^ (q & 7)) << 4),
 // so both the query-major writes and the unit-major read-back are conflict-free.  With a
 // 128-byte-aligned row the XOR folds into the address: (row | rot) ^ (u << 4).
-// Read-back of such a buffer and coalesced store: 8 lanes cover one query's 128 bytes,
-// 4 queries per instruction.
-//   ld_base : this lane's read address for iteration 0;  g : its global address for iteration 0
-template <bool FULL>
-__device__ __forceinline__ void flush128(uint32_t ld_base, char *g, long long stride4, int sub, int nq, bool lane_ok,
-                                         uint64_t pol) {
-#pragma unroll
-  for (int it = 0; it < 8; ++it) {
-    const uint4 val = lds16((ld_base ^ (((4 * it) & 7) << 4)) + it * 512);
-    if (FULL || (lane_ok && 4 * it + sub < nq)) stg16_hint(g, val, pol);
-    g += stride4;
-  }
-}
-// Same for 64-byte query rows (bf16 level 1): unit u of query q at q*64 + ((u ^ ((q >> 1) & 3)) << 4);
-// 4 lanes per query, 8 queries per instruction.
-template <bool FULL>
-__device__ __forceinline__ void flush64(uint32_t ld_base, char *g, long long stride8, int sub, int nq, bool lane_ok,
-                                        uint64_t pol) {
-#pragma unroll
-  for (int it = 0; it < 4; ++it) {
-    const uint4 val = lds16(ld_base + it * 512);
-    if (FULL || (lane_ok && 8 * it + sub < nq)) stg16_hint(g, val, pol);
-    g += stride8;
-  }
-}
-
+// Read-back of such a buffer and coalesced store, one full 32-byte sector per lane (st.global.v8): 4 lanes cover one
+// query's 128 bytes, 8 queries per instruction.  `sbuf`: the buffer's base; lane = (query within 8) * 4 + unit pair;
+// g: this lane's global address for its first query.  (With 16-byte stores the kernel was 4 % slower.)
 __device__ __forceinline__ void named_bar_arrive(uint32_t id, uint32_t count) {
   asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory");
 }
@@ -196,6 +174,36 @@ __device__ __forceinline__ void stg32_hint(void *dst, const uint4 &a, const uint
   asm volatile("st.global.L2::cache_hint.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8}, %9;" ::"l"(dst), "r"(a.x), "r"(a.y),
                "r"(a.z), "r"(a.w), "r"(b.x), "r"(b.y), "r"(b.z), "r"(b.w), "l"(policy)
                : "memory");
+}
+
+template <bool FULL>
+__device__ __forceinline__ void flush128_v8(uint32_t sbuf, int lane, char *g, long long stride8, int nq, bool lane_ok,
+                                            uint64_t pol) {
+  const int up = lane & 3, sub8 = lane >> 2;
+#pragma unroll
+  for (int it = 0; it < 4; ++it) {
+    const int q = 8 * it + sub8;
+    const uint32_t row = sbuf + q * 128;
+    const uint4 a = lds16(row + (((2 * up) ^ (q & 7)) << 4));
+    const uint4 b = lds16(row + (((2 * up + 1) ^ (q & 7)) << 4));
+    if (FULL || (lane_ok && q < nq)) stg32_hint(g, a, b, pol);
+    g += stride8;
+  }
+}
+
+// the same for 64-byte query rows (2-byte level 1): 2 lanes per query, 16 queries per instruction
+template <bool FULL>
+__device__ __forceinline__ void flush64_v8(uint32_t lbuf, int lane, char *g, long long stride16, int nq, uint64_t pol) {
+  const int up = lane & 1, sub16 = lane >> 1;
+#pragma unroll
+  for (int it = 0; it < 2; ++it) {
+    const int q = 16 * it + sub16;
+    const uint32_t row = lbuf + q * 64;
+    const uint4 a = lds16(row + (((2 * up) ^ ((q >> 1) & 3)) << 4));
+    const uint4 b = lds16(row + (((2 * up + 1) ^ ((q >> 1) & 3)) << 4));
+    if (FULL || q < nq) stg32_hint(g, a, b, pol);
+    g += stride16;
+  }
 }
 
 // ---------------------------------------------------------------- the kernel
@@ -332,16 +340,10 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
     const uint32_t sbuf = sStage + (warp - EPI_WARP0) * STAGE_BYTES_PER_WARP;   // level-0 step buffer
     const uint32_t lbuf = sbuf + STEP_BYTES;                                    // level-1 buffer
     const int L = p.num_levels;
-    // per-lane constants of the staging buffers (see flush128 / flush64)
+    // per-lane constants of the staging buffers (see flush128_v8 / flush64_v8)
     const uint32_t st_base = (sbuf + lane * 128) | ((lane & 7) << 4);           // write: unit u at st_base ^ (u << 4)
-    const int u8 = lane & 7, sub4 = lane >> 3;
-    const uint32_t ld_base = (sbuf + sub4 * 128) | ((u8 ^ sub4) << 4);
-    const int l0_tile = ES == 2 ? (u8 >> 2) : (u8 >> 1);                        // tile (of the group's) holding unit u8
-    const int l0_off = ES == 2 ? u8 * 16 : (u8 >> 1) * 64 + (u8 & 1) * 16;      // its byte offset in the chunk
     // level 1: bf16 = 4 units (one tile) per query, 64-byte rows; fp32 = 8 units (two tiles), 128-byte rows
     const uint32_t l1_st = ES == 2 ? ((lbuf + lane * 64) | (((lane >> 1) & 3) << 4)) : ((lbuf + lane * 128) | ((lane & 7) << 4));
-    const int u4 = lane & 3, sub8 = lane >> 2;
-    const uint32_t l1_ld = ES == 2 ? (lbuf + sub8 * 64 + ((u4 ^ ((sub8 >> 1) & 3)) << 4)) : ((lbuf + sub4 * 128) | ((u8 ^ sub4) << 4));
     const uint64_t pol_out = l2_policy_evict_first();
 
     TileWalk walk;
@@ -369,7 +371,11 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
       const int nt0 = min(S::L0_GT, p.tiles_x[0] - txg);
       const bool full0 = nq == 32 && nt0 == S::L0_GT;
       const long long slab0B = p.slab[0] * ES;
-      char *g0 = (char *)p.lvl[0] + ((long long)(y0 >> 2) * p.tiles_x[0] + txg) * 64 + (slab_q0 + sub4) * slab0B + l0_off;
+      // level-0 flush: lane = (query within 8) * 4 + pair of units; a pair is 32 contiguous bytes of one tile
+      const int up4 = lane & 3;
+      char *g0 = (char *)p.lvl[0] + ((long long)(y0 >> 2) * p.tiles_x[0] + txg) * 64 + (slab_q0 + (lane >> 2)) * slab0B +
+                 (ES == 2 ? up4 * 32 : up4 * 64);
+      const bool pair_ok = (ES == 2 ? (up4 >> 1) : up4) < nt0;
       const long long tile_row0B = (long long)p.tiles_x[0] * 64;
 
       // ---- accumulator -> registers, then hand it back at once
@@ -478,8 +484,8 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
           // bf16: step = one row of tiles; fp32: step = two of the four rows of a row of tiles
           if ((y0 >> 2) + (rp >> 1) < p.tiles_y[0] && nt0 > 0) {
             char *g = g0 + (rp >> 1) * tile_row0B + (ES == 2 ? 0 : (rp & 1) * 32);
-            if (full0) flush128<true>(ld_base, g, 4 * slab0B, sub4, nq, true, pol_out);
-            else flush128<false>(ld_base, g, 4 * slab0B, sub4, nq, l0_tile < nt0, pol_out);
+            if (full0) flush128_v8<true>(sbuf, lane, g, 8 * slab0B, nq, true, pol_out);
+            else flush128_v8<false>(sbuf, lane, g, 8 * slab0B, nq, pair_ok, pol_out);
           }
           __syncwarp();
         }
@@ -493,13 +499,13 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
           const long long slab1B = p.slab[1] * ES;
           char *g1 = (char *)p.lvl[1] + ((long long)(y0 >> 3) * p.tiles_x[1] + tx1) * 64;
           if (ES == 2) {
-            g1 += (slab_q0 + sub8) * slab1B + u4 * 16;
-            if (nq == 32) flush64<true>(l1_ld, g1, 8 * slab1B, sub8, nq, true, pol_out);
-            else flush64<false>(l1_ld, g1, 8 * slab1B, sub8, nq, true, pol_out);
+            g1 += (slab_q0 + (lane >> 1)) * slab1B + (lane & 1) * 32;
+            if (nq == 32) flush64_v8<true>(lbuf, lane, g1, 16 * slab1B, nq, pol_out);
+            else flush64_v8<false>(lbuf, lane, g1, 16 * slab1B, nq, pol_out);
           } else {
-            g1 += (slab_q0 + sub4) * slab1B + u8 * 16;       // unit u8 = tile u8 >> 2, row u8 & 3
-            if (nq == 32 && nt1 == 2) flush128<true>(l1_ld, g1, 4 * slab1B, sub4, nq, true, pol_out);
-            else flush128<false>(l1_ld, g1, 4 * slab1B, sub4, nq, (u8 >> 2) < nt1, pol_out);
+            g1 += (slab_q0 + (lane >> 2)) * slab1B + (lane & 3) * 32;     // pair of units = rows 2k, 2k+1 of tile (lane & 3) >> 1
+            if (nq == 32 && nt1 == 2) flush128_v8<true>(lbuf, lane, g1, 8 * slab1B, nq, true, pol_out);
+            else flush128_v8<false>(lbuf, lane, g1, 8 * slab1B, nq, ((lane & 3) >> 1) < nt1, pol_out);
           }
         }
         __syncwarp();
