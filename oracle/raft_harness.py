@@ -90,7 +90,6 @@ class TorchCorrBlock:
         return self._P.lookup(self.pyr, coords, self.radius)
 
 
-@torch.no_grad()
 def update_after_convc1(update, net, inp, cor, flow):
     """BasicUpdateBlock.forward (core/update.py:131-139) with BasicMotionEncoder.forward (:88-95) inlined and its first
     line, `cor = F.relu(self.convc1(corr))`, already done by the caller: `cor` is that activation.  Every layer is the
@@ -105,6 +104,7 @@ def update_after_convc1(update, net, inp, cor, flow):
     return net, 0.25 * update.mask(net), update.flow_head(net)
 
 
+@torch.no_grad()
 def raft_forward(nets, image1, image2, iters=12, corr_cls=TorchCorrBlock, last_only=True, upsample_fn=None,
                  mixed_precision=False, fuse_convc1=False):
     """RAFT.forward(test_mode=True) (core/raft.py:86-144) -> (flow_low, flow_up).  mixed_precision wraps the three
