@@ -27,6 +27,7 @@
 // stage index and phase incrementally (no divisions): their per-stage overhead
 // is on the critical path of the tensor pipe.
 #include <cuda.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "tc_ptx.cuh"
@@ -40,7 +41,7 @@ constexpr int BK = 64;           // bf16 elements per k-block (128 bytes = swizz
 constexpr int UMMA_K = 16;       // bf16 elements per MMA (32 bytes); kind::tf32: 8 fp32, the same 32 bytes
 constexpr int A_KB_BYTES = BM * 128;   // 16 KB
 constexpr int B_ST_BYTES = BN * 128;   // 32 KB
-constexpr int MAX_STAGES = 4;
+constexpr int MAX_STAGES = 8;
 constexpr int EPI_WARP0 = 2;
 constexpr int EPI_WARPS = 8;           // two groups of four
 constexpr int TC_THREADS = 32 * (EPI_WARP0 + EPI_WARPS);
@@ -48,7 +49,9 @@ constexpr int GW = TB_W / 2;           // block columns per epilogue group (16)
 
 struct TcParams {
   int B, N, MT, NT, nbx, KB, num_levels, stages;
+  int MTW;                          // query-block units the tile walk counts per pair: MT, or ceil(MT / 2) for CTA pairs
   int group_pairs, num_groups;      // pairs processed together (see TileWalk)
+  int debug;                        // TEMP: attribution switches (RC_TC_DEBUG)
   int b_nhwc;                       // fmap2 operand is plain NHWC [B][H][W][D]: its 8x32 blocks are cut by a 4-D TMA box
   uint32_t idesc;                   // instruction descriptor (operand format: bf16, f16 or tf32)
   float scale;                      // what is left of 1/sqrt(D) after the pack's exact power-of-two part
@@ -67,17 +70,21 @@ struct TcParams {
 struct TileWalk {
   int grp, left;              // current group, tiles left in this CTA's range of it
   int b, m, n, by, bx;        // the next tile; (by, bx) = n's block coordinates
-  __device__ __forceinline__ void init() { grp = -1; left = 0; b = m = n = by = bx = 0; }
+  int wid, nw;                // this walker and the number of walkers (CTAs, or CTA pairs: both CTAs of a pair walk alike)
+  __device__ __forceinline__ void init(int walker, int walkers) {
+    grp = -1; left = 0; b = m = n = by = bx = 0;
+    wid = walker; nw = walkers;
+  }
   __device__ __forceinline__ bool next(const TcParams &p, int &ob, int &om, int &on, int &oby, int &obx) {
     while (left == 0) {
       ++grp;
       if (grp >= p.num_groups) return false;
       const int pair0 = grp * p.group_pairs;
       const int np = min(p.group_pairs, p.B - pair0);
-      const int tpp = p.MT * p.NT;
+      const int tpp = p.MTW * p.NT;
       const long long tot = (long long)np * tpp;
-      const int t0 = (int)(tot * blockIdx.x / gridDim.x);
-      const int t1 = (int)(tot * (blockIdx.x + 1) / gridDim.x);
+      const int t0 = (int)(tot * wid / nw);
+      const int t1 = (int)(tot * (wid + 1) / nw);
       left = t1 - t0;
       const int pb = t0 / tpp, r = t0 - pb * tpp;
       b = pair0 + pb;
@@ -91,7 +98,7 @@ struct TileWalk {
     if (++bx == p.nbx) { bx = 0; ++by; }
     if (++n == p.NT) {
       n = 0; by = 0; bx = 0;
-      if (++m == p.MT) { m = 0; ++b; }
+      if (++m == p.MTW) { m = 0; ++b; }
     }
     return true;
   }
@@ -102,14 +109,11 @@ struct TileWalk {
 // PTX wrappers (mbarrier, TMA, tcgen05, L2 policies): tc_ptx.cuh
 using namespace tc;
 
-// kind::f16: D = F32 (bit 4), A = B = BF16 (bits 7, 10), both K-major, N>>3 at 17, M>>4 at 24
-constexpr uint32_t IDESC_BF16 = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) |
-                                ((uint32_t)(BM >> 4) << 24);
-// kind::f16 with IEEE-half operands: format code 0
-constexpr uint32_t IDESC_F16 = (1u << 4) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
-// kind::tf32: the same with A = B = TF32 (format code 2)
-constexpr uint32_t IDESC_TF32 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) |
-                                ((uint32_t)(BM >> 4) << 24);
+// Instruction descriptor: D = F32 (bit 4), operand format of A and B at bits 7 and 10 (kind::f16: 0 = IEEE half,
+// 1 = bf16; kind::tf32: 2 = tf32), both K-major, N >> 3 at bit 17, M >> 4 at bit 24 (M = 256 for a CTA pair).
+constexpr uint32_t make_idesc(uint32_t fmt, int M) {
+  return (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
 
 // ---------------------------------------------------------------- epilogue staging
 // An epilogue thread owns one query (TMEM lane) and an 8 x 16 sub-block of the
@@ -143,6 +147,10 @@ struct Stg<float> {
 constexpr int STEP_BYTES = 32 * 128;      // per-warp level-0 step buffer
 constexpr int L1BUF_BYTES = 32 * 128;     // per-warp level-1 buffer (bf16 uses half)
 constexpr int STAGE_BYTES_PER_WARP = STEP_BYTES + L1BUF_BYTES;
+// The same for the epilogue that stores with TMA (CTA pairs, 2-byte storage): two level-0 step buffers (a step's bulk
+// store drains while the next step is computed), two level-1 buffers (tile parity), 1 KB for the level-2/3 exchange.
+constexpr int TS_L1_OFF = 2 * STEP_BYTES, TS_L1_BYTES = 2048, TS_XQ_OFF = TS_L1_OFF + 2 * TS_L1_BYTES;
+constexpr int TS_BYTES_PER_WARP = TS_XQ_OFF + 1024;          // 13 KB
 
 __device__ __forceinline__ void sts16(uint32_t addr, uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
@@ -210,23 +218,35 @@ __device__ __forceinline__ void flush64_v8(uint32_t lbuf, int lane, char *g, lon
 // TF32 = false: bf16 operands (kind::f16), the query operand stationary in shared memory.
 // TF32 = true:  fp32 operands read as tf32 (kind::tf32, 32 channels per 128-byte k-block).  Twice the operand bytes
 //               do not fit next to the epilogue staging as a stationary operand, so the 16 KB query k-block rides
-//               in the ring slot with its 32 KB target k-block (one expect_tx, two TMA loads per slot).
-template <typename VolT, bool SCALE, bool TF32>
+//               in the ring slot with its target k-block (one expect_tx, two TMA loads per slot).
+// PAIR = true:  two CTAs of a cluster (one TPC) work as a pair on ONE MMA of 256 queries x 256 targets
+//               (tcgen05 cta_group::2): CTA r of the pair owns query block 2 m + r (its own A operand and its own
+//               128 x 256 accumulator: the epilogue is the single-CTA one) and loads only HALF of every target k-block
+//               (block rows 4 r .. 4 r + 3: 16 KB instead of 32 KB).  The operand stream out of L2, the larger part of
+//               what this kernel moves through L2, is halved.  The leader (rank 0) issues the MMAs; loads of both
+//               CTAs count on the leader's "full" barriers; the leader's commits are multicast to both CTAs' "empty" and
+//               "accumulator full" barriers; both epilogues arrive on the leader's "accumulator empty" barrier.
+template <typename VolT, bool SCALE, bool TF32, bool PAIR>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                        const __grid_constant__ CUtensorMap map_l0, const __grid_constant__ CUtensorMap map_l1,
                         const TcParams p) {
   using S = Stg<VolT>;
   constexpr int ES = (int)sizeof(VolT);
+  constexpr bool TMAST = PAIR && ES == 2;            // levels 0 and 1 leave through TMA tensor stores (map_l0, map_l1)
+  constexpr uint32_t WSTAGE = TMAST ? TS_BYTES_PER_WARP : STAGE_BYTES_PER_WARP;
   constexpr int BKE = TF32 ? BK / 2 : BK;                                   // operand elements per k-block
-  constexpr uint32_t SLOT = TF32 ? A_KB_BYTES + B_ST_BYTES : B_ST_BYTES;    // bytes per ring slot
+  constexpr uint32_t B_SLOT = PAIR ? B_ST_BYTES / 2 : B_ST_BYTES;           // target bytes per ring slot of this CTA
+  constexpr uint32_t SLOT = TF32 ? A_KB_BYTES + B_SLOT : B_SLOT;            // bytes per ring slot
+  constexpr uint32_t CTAS = PAIR ? 2 : 1;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // carve (operand offsets are multiples of 1024)
   uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const uint32_t sA = smem_u32(smem);
   const uint32_t sB = TF32 ? sA : sA + p.KB * A_KB_BYTES;
   const uint32_t sStage = sB + p.stages * SLOT;
-  const uint32_t sBar = sStage + EPI_WARPS * STAGE_BYTES_PER_WARP;
-  uint32_t *tmem_slot = (uint32_t *)(smem + (sBar - sA) + 128);
+  const uint32_t sBar = sStage + EPI_WARPS * WSTAGE;
+  uint32_t *tmem_slot = (uint32_t *)(smem + (sBar - sA) + 240);
   // barrier table (8 bytes each)
   const uint32_t bar_a_full = sBar, bar_a_empty = sBar + 8;
   const uint32_t bar_b_full = sBar + 16;                        // [stages]
@@ -235,6 +255,9 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
   const uint32_t bar_t_empty = bar_t_full + 16;                 // [2]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = PAIR ? cluster_ctarank() : 0u;          // 0 = the pair's leader
+  const int walker = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int walkers = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
 
   if (warp == 0 && lane == 0) {
     mbar_init(bar_a_full, 1);
@@ -245,16 +268,22 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(bar_t_full + 8 * s, 1);
-      mbar_init(bar_t_empty + 8 * s, EPI_WARPS);
+      mbar_init(bar_t_empty + 8 * s, CTAS * EPI_WARPS);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(tmem_slot)));
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    if (PAIR) {
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(tmem_slot)));
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;");
+    } else {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(tmem_slot)));
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
   }
   fence_before();
   __syncthreads();
+  if (PAIR) cluster_sync_all();      // the peer's barriers exist before anything is sent to them
   fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -262,46 +291,62 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
     // ===================================================== TMA producer
     if (lane == 0) {
       const uint64_t pol_in = l2_policy_evict_last();
+      // where this CTA's loads report: its own "full" barriers, or the leader's
+      const uint32_t full_a = PAIR ? mapa_shared(bar_a_full, 0) : bar_a_full;
+      const uint32_t full_b = PAIR ? mapa_shared(bar_b_full, 0) : bar_b_full;
       TileWalk walk;
-      walk.init();
+      walk.init(walker, walkers);
       int b, m, n, by, bx, cur_key = -1;
       uint32_t a_par = 0;                    // parity of the A-empty phase to wait for next
       bool a_loaded = false;
       uint32_t st = 0, ph = 0;               // B ring: stage, parity of its current round
       while (walk.next(p, b, m, n, by, bx)) {
-        const int key = b * p.MT + m;
+        const int key = b * p.MTW + m;
+        const int mq = (PAIR ? 2 * m + (int)rank : m) * BM;      // first query of this CTA's block (may lie past N: zeros)
         if (!TF32 && key != cur_key) {
           if (a_loaded) { mbar_wait(bar_a_empty, a_par); a_par ^= 1; }
-          mbar_expect_tx(bar_a_full, p.KB * A_KB_BYTES);
-          for (int kb = 0; kb < p.KB; ++kb)
-            tma_load_3d(sA + kb * A_KB_BYTES, &map_a, bar_a_full, kb * BKE, m * BM, b, pol_in);
+          if (rank == 0) mbar_expect_tx(bar_a_full, CTAS * p.KB * A_KB_BYTES);
+          for (int kb = 0; kb < p.KB; ++kb) {
+            if (PAIR) tma_load_3d_2sm(sA + kb * A_KB_BYTES, &map_a, full_a, kb * BKE, mq, b, pol_in);
+            else tma_load_3d(sA + kb * A_KB_BYTES, &map_a, bar_a_full, kb * BKE, mq, b, pol_in);
+          }
           a_loaded = true;
           cur_key = key;
         }
         for (int kb = 0; kb < p.KB; ++kb) {
           mbar_wait(bar_b_empty + 8 * st, ph ^ 1);
-          mbar_expect_tx(bar_b_full + 8 * st, SLOT);
-          if (TF32) tma_load_3d(sB + st * SLOT, &map_a, bar_b_full + 8 * st, kb * BKE, m * BM, b, pol_in);
-          if (!TF32 && p.b_nhwc)     // box (64 d, 32 x, 8 y): lands in the block order the pack would have written; outside the map: zeros
-            tma_load_4d_hint(sB + st * SLOT, &map_b, bar_b_full + 8 * st, kb * BKE, bx * TB_W, by * TB_H, b, pol_in);
-          else
-            tma_load_3d(sB + st * SLOT + (TF32 ? A_KB_BYTES : 0), &map_b, bar_b_full + 8 * st, kb * BKE, n * BN, b, pol_in);
+          if (rank == 0) mbar_expect_tx(bar_b_full + 8 * st, CTAS * SLOT);
+          const uint32_t dst = sB + st * SLOT;
+          if (PAIR) {
+            const uint32_t fb = full_b + 8 * st;
+            if (TF32) tma_load_3d_2sm(dst, &map_a, fb, kb * BKE, mq, b, pol_in);
+            if (!TF32 && p.b_nhwc)   // box (64 d, 32 x, 4 y): this CTA's four rows of the 8x32 block
+              tma_load_4d_2sm(dst, &map_b, fb, kb * BKE, bx * TB_W, by * TB_H + (int)rank * (TB_H / 2), b, pol_in);
+            else
+              tma_load_3d_2sm(dst + (TF32 ? A_KB_BYTES : 0), &map_b, fb, kb * BKE, n * BN + (int)rank * (BN / 2), b, pol_in);
+          } else {
+            if (TF32) tma_load_3d(dst, &map_a, bar_b_full + 8 * st, kb * BKE, mq, b, pol_in);
+            if (!TF32 && p.b_nhwc)     // box (64 d, 32 x, 8 y): lands in the block order the pack would have written; outside the map: zeros
+              tma_load_4d_hint(dst, &map_b, bar_b_full + 8 * st, kb * BKE, bx * TB_W, by * TB_H, b, pol_in);
+            else
+              tma_load_3d(dst + (TF32 ? A_KB_BYTES : 0), &map_b, bar_b_full + 8 * st, kb * BKE, n * BN, b, pol_in);
+          }
           if (++st == (uint32_t)p.stages) { st = 0; ph ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
-    // ===================================================== MMA issuer
-    if (lane == 0) {
+    // ===================================================== MMA issuer (of a pair: the leader's)
+    if (lane == 0 && rank == 0) {
       TileWalk walk;
-      walk.init();
+      walk.init(walker, walkers);
       int b, m, n, by, bx, cur_key = -1;
       uint32_t a_par = 0;                    // parity of the A-full phase to wait for next
       uint32_t st = 0, ph = 0;
       uint32_t i = 0;                        // tile counter: accumulator i & 1, its use number i >> 1
       const uint32_t a_lo = desc_lo(sA), b_lo = desc_lo(sB);
       while (walk.next(p, b, m, n, by, bx)) {
-        const int key = b * p.MT + m;
+        const int key = b * p.MTW + m;
         if (!TF32 && key != cur_key) {
           mbar_wait(bar_a_full, a_par);
           a_par ^= 1;
@@ -319,26 +364,34 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
           const uint32_t bl = b_lo + ((st * SLOT + (TF32 ? A_KB_BYTES : 0)) >> 4);
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; ++k) {      // four MMAs of 32 operand bytes per k-block, either kind
-            if (TF32)
-              umma_tf32(d_tmem, desc_make(al + k * ((UMMA_K * 2) >> 4)), desc_make(bl + k * ((UMMA_K * 2) >> 4)),
-                        IDESC_TF32, (kb | k) != 0);
-            else      // kind::f16: bf16 or IEEE-half operands, told apart by the descriptor's format fields
-              umma_bf16(d_tmem, desc_make(al + k * ((UMMA_K * 2) >> 4)), desc_make(bl + k * ((UMMA_K * 2) >> 4)),
-                        p.idesc, (kb | k) != 0);
+            const uint64_t ad = desc_make(al + k * ((UMMA_K * 2) >> 4)), bd = desc_make(bl + k * ((UMMA_K * 2) >> 4));
+            const uint32_t accum = (kb | k) != 0;
+            if (PAIR) {
+              if (TF32) umma_tf32_2sm(d_tmem, ad, bd, p.idesc, accum);
+              else umma_bf16_2sm(d_tmem, ad, bd, p.idesc, accum);
+            } else {
+              if (TF32) umma_tf32(d_tmem, ad, bd, p.idesc, accum);
+              else umma_bf16(d_tmem, ad, bd, p.idesc, accum);      // bf16 or IEEE-half operands: the descriptor's format fields
+            }
           }
-          umma_commit(bar_b_empty + 8 * st);   // frees the B stage when these MMAs retire
+          if (PAIR) umma_commit_2sm(bar_b_empty + 8 * st);   // frees the stage (in both CTAs) when these MMAs retire
+          else umma_commit(bar_b_empty + 8 * st);
           if (++st == (uint32_t)p.stages) { st = 0; ph ^= 1; }
         }
-        umma_commit(bar_t_full + 8 * acc);     // accumulator ready
-        if (!TF32 && walk.a_changes(b, m)) umma_commit(bar_a_empty);   // last use of this A operand
+        if (PAIR) umma_commit_2sm(bar_t_full + 8 * acc);     // accumulator ready
+        else umma_commit(bar_t_full + 8 * acc);
+        if (!TF32 && walk.a_changes(b, m)) {                 // last use of this A operand
+          if (PAIR) umma_commit_2sm(bar_a_empty);
+          else umma_commit(bar_a_empty);
+        }
       }
     }
   } else {
     // ===================================================== epilogue (2 groups x 4 warps)
     const int quarter = warp & 3;                 // TMEM lanes [32*quarter, +32)
     const int group = (warp - EPI_WARP0) >> 2;    // block columns 16*group .. +15
-    const uint32_t sbuf = sStage + (warp - EPI_WARP0) * STAGE_BYTES_PER_WARP;   // level-0 step buffer
-    const uint32_t lbuf = sbuf + STEP_BYTES;                                    // level-1 buffer
+    const uint32_t sbuf = sStage + (warp - EPI_WARP0) * WSTAGE;                 // level-0 step buffer(s)
+    const uint32_t lbuf = sbuf + (TMAST ? TS_L1_OFF : STEP_BYTES);              // level-1 buffer(s)
     const int L = p.num_levels;
     // per-lane constants of the staging buffers (see flush128_v8 / flush64_v8)
     const uint32_t st_base = (sbuf + lane * 128) | ((lane & 7) << 4);           // write: unit u at st_base ^ (u << 4)
@@ -346,8 +399,10 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
     const uint32_t l1_st = ES == 2 ? ((lbuf + lane * 64) | (((lane >> 1) & 3) << 4)) : ((lbuf + lane * 128) | ((lane & 7) << 4));
     const uint64_t pol_out = l2_policy_evict_first();
 
+    const uint32_t t_empty = PAIR ? mapa_shared(bar_t_empty, 0) : bar_t_empty;   // the MMA issuer's barrier (pair: the leader's)
+
     TileWalk walk;
-    walk.init();
+    walk.init(walker, walkers);
     int b, m, n, by, bx;
     uint32_t i = 0;
     while (walk.next(p, b, m, n, by, bx)) {
@@ -356,7 +411,7 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
       ++i;
       const int x0 = bx * TB_W, y0 = by * TB_H;
       const int xg = x0 + group * GW;                  // first map column of this group's sub-block
-      const int qw = m * BM + quarter * 32;            // first query of this warp
+      const int qw = (PAIR ? 2 * m + (int)rank : m) * BM + quarter * 32;   // first query of this warp (past N: nothing is stored)
       const long long slab_q0 = (long long)b * p.N + qw;    // slab index of this warp's first query
       const int nq = min(32, p.N - qw);                     // valid queries of this warp (may be <= 0)
 
@@ -388,7 +443,12 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
       tmem_ld_wait();
       fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(bar_t_empty + 8 * acc);
+      if (lane == 0) {
+        if (PAIR) mbar_arrive_cluster(t_empty + 8 * acc);
+        else mbar_arrive(bar_t_empty + 8 * acc);
+      }
+      const int dbg = p.debug;
+      if (dbg & 8) { asm volatile("" ::"r"(raw[0][0]), "r"(raw[7][15])); continue; }
 
       float p1prev[8], p2prev[4];
       uint32_t l2w[4] = {0u, 0u, 0u, 0u}, l3w = 0u;     // 2-byte storage: this thread's level-2 rows and level-3 cells, packed
@@ -402,12 +462,19 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
           if (SCALE) { v0[k] *= p.scale; v1[k] *= p.scale; }
         }
         // ---- level 0 units of block rows 2rp, 2rp+1
-        if (ES == 2) {
+        if (TMAST && !(rp & 1)) {
+          // the bulk store that last read this step buffer (and, at the start of a tile, this tile parity's level-1
+          // buffer) has to be done with shared memory: all but the newest group
+          if (lane == 0) bulk_wait_read<1>();
+          __syncwarp();
+        }
+        if (ES == 2 && !(dbg & 4)) {
           const int r = (2 * rp) & 3;                    // row inside the tile
+          const uint32_t sb = TMAST ? st_base + (rp >> 1) * STEP_BYTES : st_base;
 #pragma unroll
           for (int k = 0; k < 2; ++k) {
-            put_unit<VolT>(st_base ^ ((k * 4 + r) << 4), v0 + 8 * k);
-            put_unit<VolT>(st_base ^ ((k * 4 + r + 1) << 4), v1 + 8 * k);
+            put_unit<VolT>(sb ^ ((k * 4 + r) << 4), v0 + 8 * k);
+            put_unit<VolT>(sb ^ ((k * 4 + r + 1) << 4), v1 + 8 * k);
           }
         } else {
 #pragma unroll
@@ -426,7 +493,7 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
         if (L > 1) {
           // level-1 row rp of the sub-block: bf16 one unit (row rp of its tile), fp32 two (tiles 0, 1)
           if (ES == 2) {
-            put_unit<VolT>(l1_st ^ (rp << 4), p1);
+            put_unit<VolT>((TMAST ? l1_st + (acc * TS_L1_BYTES) : l1_st) ^ (rp << 4), p1);
           } else {
             put_unit<VolT>(l1_st ^ (rp << 4), p1);
             put_unit<VolT>(l1_st ^ ((4 + rp) << 4), p1 + 4);
@@ -479,12 +546,26 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
         }
 
         // ---- a level-0 step is complete: read it back query by query, coalesced stores
-        if (ES == 4 || (rp & 1)) {
+        if (TMAST) {
+          if (rp & 1) {
+            // this step's rows of tiles [32 queries][2 tiles x 64 B] sit in the step buffer in the 128-byte swizzle:
+            // one tensor store (box clipped at the end of the map's row of tiles, its last tile row and query), asynchronous
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) {
+              if (!(dbg & 3)) tma_store_4d(&map_l0, sbuf + (rp >> 1) * STEP_BYTES, txg * 32, (y0 >> 2) + (rp >> 1), qw, b, pol_out);
+              if (rp == 3 && L > 1 && !(dbg & 3))     // and the tile's level-1 cells: [32 queries][64 B], 64-byte swizzle
+                tma_store_4d(&map_l1, lbuf + acc * TS_L1_BYTES, ((xg >> 1) / S::TW) * 32, y0 >> 3, qw, b, pol_out);
+              bulk_commit();
+            }
+          }
+        } else if (ES == 4 || (rp & 1)) {
           __syncwarp();
           // bf16: step = one row of tiles; fp32: step = two of the four rows of a row of tiles
-          if ((y0 >> 2) + (rp >> 1) < p.tiles_y[0] && nt0 > 0) {
+          if ((y0 >> 2) + (rp >> 1) < p.tiles_y[0] && nt0 > 0 && !(dbg & 2)) {
             char *g = g0 + (rp >> 1) * tile_row0B + (ES == 2 ? 0 : (rp & 1) * 32);
-            if (full0) flush128_v8<true>(sbuf, lane, g, 8 * slab0B, nq, true, pol_out);
+            if (dbg & 1) flush128_v8<false>(sbuf, lane, g, 8 * slab0B, 0, pair_ok, pol_out);
+            else if (full0) flush128_v8<true>(sbuf, lane, g, 8 * slab0B, nq, true, pol_out);
             else flush128_v8<false>(sbuf, lane, g, 8 * slab0B, nq, pair_ok, pol_out);
           }
           __syncwarp();
@@ -492,10 +573,10 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
       }
 
       // ---- level-1 cells of the sub-block
-      if (L > 1) {
+      if (!TMAST && L > 1) {
         const int tx1 = (xg >> 1) / S::TW;
         const int nt1 = min(S::L1_GT, p.tiles_x[1] - tx1);
-        if ((y0 >> 3) < p.tiles_y[1] && nt1 > 0) {
+        if ((y0 >> 3) < p.tiles_y[1] && nt1 > 0 && !(dbg & 3)) {
           const long long slab1B = p.slab[1] * ES;
           char *g1 = (char *)p.lvl[1] + ((long long)(y0 >> 3) * p.tiles_x[1] + tx1) * 64;
           if (ES == 2) {
@@ -517,8 +598,8 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
       // more write traffic than the kernel has output).  Group 1 hands its halves to group 0 through the unused half
       // of its level-1 buffer ("full" = named barrier 1 + quarter, "empty" = 5 + quarter, 64 threads each: the
       // arriving warp and the waiting one); group 0 stores whole sectors.
-      if (ES == 2 && L > 2) {
-        const uint32_t xq = sStage + (((warp - EPI_WARP0) & 3) + 4) * STAGE_BYTES_PER_WARP + STEP_BYTES + 2048 + lane * 32;   // in the group-1 warp's buffer
+      if (ES == 2 && L > 2 && !(dbg & 3)) {
+        const uint32_t xq = sStage + (((warp - EPI_WARP0) & 3) + 4) * WSTAGE + (TMAST ? TS_XQ_OFF : STEP_BYTES + 2048) + lane * 32;   // in the group-1 warp's buffer
         if (group == 1) {
           if (!first_tile) named_bar_sync(5 + quarter, 64);
           sts16(xq, l2w[0], l2w[1], l2w[2], l2w[3]);
@@ -547,13 +628,19 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
         }
       }
     }
+    if (TMAST) {
+      if (lane == 0) bulk_wait_all();      // shared memory stays until the last stores have read it
+      __syncwarp();
+    }
   }
 
   fence_before();
   __syncthreads();
+  if (PAIR) cluster_sync_all();      // neither CTA leaves while the other may still signal its barriers or use its operands
   fence_after();
   if (warp == 1) {
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base));
+    if (PAIR) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, 512;" ::"r"(tmem_base));
+    else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base));
   }
 }
 
@@ -593,12 +680,23 @@ int encode(CUtensorMap *map, CUtensorMapDataType dt, int rank, const void *base,
   return RC_OK;
 }
 
-template <typename VolT, bool TF32>
+// RC_BUILD_PAIR=0 in the environment selects the single-CTA kernel (kept for A/B timing and for devices or contexts that
+// cannot co-schedule two CTAs of a cluster); read once.
+bool pairs_enabled() {
+  static const bool on = [] {
+    const char *e = getenv("RC_BUILD_PAIR");
+    return !(e && e[0] == '0');
+  }();
+  return on;
+}
+
+template <typename VolT, bool TF32, bool PAIR>
 int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, const rc_layout &lay,
                VolT *pyr, bool half_operands, bool nhwc, cudaStream_t s) {
   constexpr int BKE = TF32 ? BK / 2 : BK;
   constexpr int OPB = TF32 ? 4 : 2;                 // operand bytes per element
-  constexpr size_t SLOT = TF32 ? A_KB_BYTES + B_ST_BYTES : B_ST_BYTES;
+  constexpr size_t B_SLOT = PAIR ? B_ST_BYTES / 2 : B_ST_BYTES;
+  constexpr size_t SLOT = TF32 ? A_KB_BYTES + B_SLOT : B_SLOT;
   const int N = H * W;
   const int L = lay.num_levels;
   if (L > 4) {
@@ -613,10 +711,11 @@ int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, con
   p.B = B;
   p.N = N;
   p.MT = ceil_div(N, BM);
+  p.MTW = PAIR ? ceil_div(p.MT, 2) : p.MT;
   p.nbx = ceil_div(W, TB_W);
   p.NT = p.nbx * ceil_div(H, TB_H);
   p.KB = ceil_div(D, BKE);
-  p.idesc = TF32 ? IDESC_TF32 : half_operands ? IDESC_F16 : IDESC_BF16;
+  p.idesc = make_idesc(TF32 ? 2u : half_operands ? 0u : 1u, PAIR ? 2 * BM : BM);
   const CUtensorMapDataType op_type = TF32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
                                       : half_operands ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
   p.num_levels = L;
@@ -624,6 +723,7 @@ int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, con
   split_scale(D, &pre_scale, &p.scale);      // pre_scale was applied to fmap1 by the pack
   if (nhwc) p.scale = 1.0f / sqrtf((float)D);   // caller's features: unscaled, the whole factor goes to the epilogue
   p.b_nhwc = nhwc ? 1 : 0;
+  { const char *e = getenv("RC_TC_DEBUG"); p.debug = e ? atoi(e) : 0; }
   if (nhwc && (TF32 || D % BKE != 0)) {
     set_error("NHWC feature input needs 16-bit operands and D %% 64 == 0 (got D = %d)", D);
     return RC_EINVAL;
@@ -643,7 +743,9 @@ int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, con
   RC_CUDA(cudaGetDevice(&dev));
   RC_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   RC_CUDA(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
-  const size_t fixed = (TF32 ? 0 : (size_t)p.KB * A_KB_BYTES) + (size_t)EPI_WARPS * STAGE_BYTES_PER_WARP + 256 + 1024;
+  constexpr bool TMAST = PAIR && sizeof(VolT) == 2;
+  const size_t fixed = (TF32 ? 0 : (size_t)p.KB * A_KB_BYTES) +
+                       (size_t)EPI_WARPS * (TMAST ? TS_BYTES_PER_WARP : STAGE_BYTES_PER_WARP) + 256 + 1024;
   p.stages = 0;
   for (int st = MAX_STAGES; st >= 2; --st)
     if (fixed + (size_t)st * SLOT <= (size_t)max_smem) {
@@ -656,9 +758,35 @@ int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, con
   }
   const size_t smem = fixed + (size_t)p.stages * SLOT;
 
-  // pairs per group: about one query block's worth of tiles per CTA and group
-  const long long tpp = (long long)p.MT * p.NT;
-  long long gp = ((long long)p.NT * sms + tpp - 1) / tpp;
+  auto kern = p.scale == 1.f ? build_pyramid_tc_kernel<VolT, false, TF32, PAIR> : build_pyramid_tc_kernel<VolT, true, TF32, PAIR>;
+  RC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+
+  // walkers of the tile list: CTAs, or CTA pairs (as many as the device co-schedules, at most one per two SMs)
+  int walkers = sms;
+  if (PAIR) {
+    cudaLaunchConfig_t q{};
+    q.gridDim = dim3((unsigned)(sms & ~1));
+    q.blockDim = dim3(TC_THREADS);
+    q.dynamicSmemBytes = smem;
+    cudaLaunchAttribute qa{};
+    qa.id = cudaLaunchAttributeClusterDimension;
+    qa.val.clusterDim.x = 2;
+    qa.val.clusterDim.y = 1;
+    qa.val.clusterDim.z = 1;
+    q.attrs = &qa;
+    q.numAttrs = 1;
+    int clusters = 0;
+    RC_CUDA(cudaOccupancyMaxActiveClusters(&clusters, kern, &q));
+    walkers = clusters < sms / 2 ? clusters : sms / 2;
+    if (walkers < 1) {
+      set_error("the device cannot co-schedule a CTA pair of the tensor-core build (set RC_BUILD_PAIR=0)");
+      return RC_ECUDA;
+    }
+  }
+
+  // pairs per group: about one query block's worth of tiles per walker and group
+  const long long tpp = (long long)p.MTW * p.NT;
+  long long gp = ((long long)p.NT * walkers + tpp - 1) / tpp;
   if (TF32) gp = (gp + 1) / 2;            // fp32 operands: twice the bytes to keep hot in L2 per pair
   if (gp < 1) gp = 1;
   if (gp > B) gp = B;
@@ -673,27 +801,65 @@ int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, con
     int r = encode(&ma, op_type, 3, f1p, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B, "fmap1");
     if (r) return r;
   }
+  // a CTA of a pair loads half of a target block: block rows 4 r .. 4 r + 3 = 128 consecutive packed rows
   if (nhwc) {
     cuuint64_t dims[4] = {(cuuint64_t)D, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
     cuuint64_t str[3] = {(cuuint64_t)D * OPB, (cuuint64_t)W * D * OPB, (cuuint64_t)H * W * D * OPB};
-    cuuint32_t box[4] = {BKE, TB_W, TB_H, 1};
+    cuuint32_t box[4] = {BKE, TB_W, PAIR ? TB_H / 2 : TB_H, 1};
     int r = encode(&mb, op_type, 4, f2p, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B, "fmap2 (NHWC)");
     if (r) return r;
   } else {
     cuuint64_t dims[3] = {(cuuint64_t)D, (cuuint64_t)rows2, (cuuint64_t)B};
     cuuint64_t str[2] = {(cuuint64_t)D * OPB, (cuuint64_t)rows2 * D * OPB};
-    cuuint32_t box[3] = {BKE, BN, 1};
+    cuuint32_t box[3] = {BKE, PAIR ? BN / 2 : BN, 1};
     int r = encode(&mb, op_type, 3, f2p, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B, "fmap2");
     if (r) return r;
   }
 
-  auto kern = p.scale == 1.f ? build_pyramid_tc_kernel<VolT, false, TF32> : build_pyramid_tc_kernel<VolT, true, TF32>;
-  RC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  // TMA stores of levels 0 and 1: a level as [B][N][tiles_y][tiles_x * 32 elements] (a row of tiles is contiguous, 64 bytes
+  // per tile); the box is one warp's 32 queries x its tiles of one tile row (2 at level 0 = 128 bytes, 1 at level 1),
+  // clipped at the level's edges.  The box's inner extent equals the swizzle span (a 64-byte inner extent under the
+  // 128-byte swizzle is laid out differently in shared memory).
+  CUtensorMap ml0 = ma, ml1 = ma;
+  if (TMAST) {
+    for (int l = 0; l < (L > 1 ? 2 : 1); ++l) {
+      cuuint64_t dims[4] = {(cuuint64_t)lay.tiles_x[l] * 32, (cuuint64_t)lay.tiles_y[l], (cuuint64_t)N, (cuuint64_t)B};
+      cuuint64_t str[3] = {(cuuint64_t)lay.tiles_x[l] * 64, (cuuint64_t)lay.slab[l] * 2, (cuuint64_t)N * lay.slab[l] * 2};
+      cuuint32_t box[4] = {l == 0 ? 64u : 32u, 1, 32, 1};
+      int r = encode(l == 0 ? &ml0 : &ml1, CU_TENSOR_MAP_DATA_TYPE_UINT16, 4, p.lvl[l], dims, str, box,
+                     l == 0 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B, l == 0 ? "pyramid level 0" : "pyramid level 1");
+      if (r) return r;
+    }
+  }
+
   const long long group_tiles = (long long)p.group_pairs * tpp;
-  const int grid = group_tiles < sms ? (int)group_tiles : sms;
-  kern<<<grid, TC_THREADS, smem, s>>>(ma, mb, p);
+  const int used = group_tiles < walkers ? (int)group_tiles : walkers;
+  if (PAIR) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(2u * (unsigned)used);
+    cfg.blockDim = dim3(TC_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute at{};
+    at.id = cudaLaunchAttributeClusterDimension;
+    at.val.clusterDim.x = 2;
+    at.val.clusterDim.y = 1;
+    at.val.clusterDim.z = 1;
+    cfg.attrs = &at;
+    cfg.numAttrs = 1;
+    RC_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, ml0, ml1, p));
+  } else {
+    kern<<<used, TC_THREADS, smem, s>>>(ma, mb, ml0, ml1, p);
+  }
   RC_LAUNCH_CHECK("build_pyramid_tc_kernel");
   return RC_OK;
+}
+
+template <typename VolT, bool TF32>
+int build_tc_sel(const void *f1p, const void *f2p, int B, int D, int H, int W, const rc_layout &lay, VolT *pyr,
+                 bool half_operands, bool nhwc, cudaStream_t s) {
+  return pairs_enabled() ? build_tc_t<VolT, TF32, true>(f1p, f2p, B, D, H, W, lay, pyr, half_operands, nhwc, s)
+                         : build_tc_t<VolT, TF32, false>(f1p, f2p, B, D, H, W, lay, pyr, half_operands, nhwc, s);
 }
 
 }  // namespace
@@ -708,17 +874,17 @@ int launch_build_tc(const void *f1p, const void *f2p, int B, int D, int H, int W
                     int vol_dtype, int math, int nhwc, void *pyramid, cudaStream_t s) {
   const bool nh = nhwc != 0;
   if (math == RC_MATH_TF32)
-    return vol_dtype == RC_VOL_BF16  ? build_tc_t<__nv_bfloat16, true>(f1p, f2p, B, D, H, W, lay, (__nv_bfloat16 *)pyramid, false, nh, s)
-           : vol_dtype == RC_VOL_F16 ? build_tc_t<__half, true>(f1p, f2p, B, D, H, W, lay, (__half *)pyramid, false, nh, s)
-                                     : build_tc_t<float, true>(f1p, f2p, B, D, H, W, lay, (float *)pyramid, false, nh, s);
+    return vol_dtype == RC_VOL_BF16  ? build_tc_sel<__nv_bfloat16, true>(f1p, f2p, B, D, H, W, lay, (__nv_bfloat16 *)pyramid, false, nh, s)
+           : vol_dtype == RC_VOL_F16 ? build_tc_sel<__half, true>(f1p, f2p, B, D, H, W, lay, (__half *)pyramid, false, nh, s)
+                                     : build_tc_sel<float, true>(f1p, f2p, B, D, H, W, lay, (float *)pyramid, false, nh, s);
   if (math != RC_MATH_BF16 && math != RC_MATH_F16) {
     set_error("tensor-core build: math=%d is not a tensor-core mode", math);
     return RC_EINVAL;
   }
   const bool half = math == RC_MATH_F16;
-  return vol_dtype == RC_VOL_BF16  ? build_tc_t<__nv_bfloat16, false>(f1p, f2p, B, D, H, W, lay, (__nv_bfloat16 *)pyramid, half, nh, s)
-         : vol_dtype == RC_VOL_F16 ? build_tc_t<__half, false>(f1p, f2p, B, D, H, W, lay, (__half *)pyramid, half, nh, s)
-                                   : build_tc_t<float, false>(f1p, f2p, B, D, H, W, lay, (float *)pyramid, half, nh, s);
+  return vol_dtype == RC_VOL_BF16  ? build_tc_sel<__nv_bfloat16, false>(f1p, f2p, B, D, H, W, lay, (__nv_bfloat16 *)pyramid, half, nh, s)
+         : vol_dtype == RC_VOL_F16 ? build_tc_sel<__half, false>(f1p, f2p, B, D, H, W, lay, (__half *)pyramid, half, nh, s)
+                                   : build_tc_sel<float, false>(f1p, f2p, B, D, H, W, lay, (float *)pyramid, half, nh, s);
 }
 
 }  // namespace rc
