@@ -12,7 +12,8 @@ RC_ABI_VERSION = 6
 RC_STATIC_SCRATCH_BYTES = 16 << 20
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libraftcorr.so")
+# RAFTCORR_LIB: another build of the same library (tools/power_probe.py loads the attribution build this way)
+LIB_PATH = os.environ.get("RAFTCORR_LIB") or os.path.join(_HERE, "libraftcorr.so")
 
 
 class Layout(C.Structure):

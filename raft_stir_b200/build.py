@@ -41,20 +41,27 @@ def _stale(target: str, deps) -> bool:
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    """Build (if stale) and return the path of libraftcorr.so."""
+def build(force: bool = False, verbose: bool = False, attrib: bool = False) -> str:
+    """Build (if stale) and return the path of libraftcorr.so.
+
+    attrib=True builds a second, separate library under _build/attrib/ with -DRC_TC_ATTRIB: the build kernel then
+    obeys the RC_TC_DEBUG switches that turn parts of its epilogue off (timing / power attribution only, results are
+    wrong by construction).  Load it with RAFTCORR_LIB=<path>; the shipped library contains none of it."""
     nvcc = _nvcc()
-    os.makedirs(OBJ, exist_ok=True)
+    obj_dir = os.path.join(OBJ, "attrib") if attrib else OBJ
+    lib_path = os.path.join(obj_dir, "libraftcorr.so") if attrib else LIB
+    extra = ["-DRC_TC_ATTRIB"] if attrib else []
+    os.makedirs(obj_dir, exist_ok=True)
     jobs = []
     for src in SOURCES:
         s = os.path.join(CSRC, src)
-        o = os.path.join(OBJ, src.replace(".cu", ".o"))
+        o = os.path.join(obj_dir, src.replace(".cu", ".o"))
         if force or _stale(o, [s] + HEADERS):
             jobs.append((s, o))
 
     def compile_one(job):
         s, o = job
-        cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", s, "-o", o]
+        cmd = [nvcc] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-c", s, "-o", o]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"nvcc failed for {s}:\n{r.stdout}\n{r.stderr}")
@@ -65,16 +72,16 @@ def build(force: bool = False, verbose: bool = False) -> str:
             for s, log in ex.map(compile_one, jobs):
                 if verbose and log:
                     print(f"== {os.path.basename(s)}\n{log}", file=sys.stderr)
-    objs = [os.path.join(OBJ, s.replace(".cu", ".o")) for s in SOURCES]
-    if force or jobs or _stale(LIB, objs):
+    objs = [os.path.join(obj_dir, s.replace(".cu", ".o")) for s in SOURCES]
+    if force or jobs or _stale(lib_path, objs):
         cuda_lib = os.path.join(os.path.dirname(os.path.dirname(nvcc)), "lib64")
-        cmd = [nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB] + objs + [
+        cmd = [nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", lib_path] + objs + [
             "-L" + cuda_lib, "-Xlinker", "-rpath=" + cuda_lib]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
-    return LIB
+    return lib_path
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, attrib="--attrib" in sys.argv))

@@ -51,7 +51,7 @@ struct TcParams {
   int B, N, MT, NT, nbx, KB, num_levels, stages;
   int MTW;                          // query-block units the tile walk counts per pair: MT, or ceil(MT / 2) for CTA pairs
   int group_pairs, num_groups;      // pairs processed together (see TileWalk)
-  int debug;                        // TEMP: attribution switches (RC_TC_DEBUG)
+  int debug;                        // attribution switches; only read by builds with -DRC_TC_ATTRIB (tools/power_probe.py)
   int b_nhwc;                       // fmap2 operand is plain NHWC [B][H][W][D]: its 8x32 blocks are cut by a 4-D TMA box
   uint32_t idesc;                   // instruction descriptor (operand format: bf16, f16 or tf32)
   float scale;                      // what is left of 1/sqrt(D) after the pack's exact power-of-two part
@@ -447,8 +447,16 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
         if (PAIR) mbar_arrive_cluster(t_empty + 8 * acc);
         else mbar_arrive(bar_t_empty + 8 * acc);
       }
+      // Attribution builds only (python -m raft_stir_b200.build --attrib -> _build/attrib/libraftcorr.so, RC_TC_DEBUG in
+      // the environment): 1 = no global stores of levels 0/1 and no level-2/3 stores, 2 = the same, 4 = no staging
+      // writes either, 8 = the epilogue stops after its TMEM reads.  Results are wrong by construction; the shipped
+      // library compiles with dbg = 0 and none of this.
+#ifdef RC_TC_ATTRIB
       const int dbg = p.debug;
       if (dbg & 8) { asm volatile("" ::"r"(raw[0][0]), "r"(raw[7][15])); continue; }
+#else
+      constexpr int dbg = 0;
+#endif
 
       float p1prev[8], p2prev[4];
       uint32_t l2w[4] = {0u, 0u, 0u, 0u}, l3w = 0u;     // 2-byte storage: this thread's level-2 rows and level-3 cells, packed
@@ -723,7 +731,9 @@ int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, con
   split_scale(D, &pre_scale, &p.scale);      // pre_scale was applied to fmap1 by the pack
   if (nhwc) p.scale = 1.0f / sqrtf((float)D);   // caller's features: unscaled, the whole factor goes to the epilogue
   p.b_nhwc = nhwc ? 1 : 0;
+#ifdef RC_TC_ATTRIB
   { const char *e = getenv("RC_TC_DEBUG"); p.debug = e ? atoi(e) : 0; }
+#endif
   if (nhwc && (TF32 || D % BKE != 0)) {
     set_error("NHWC feature input needs 16-bit operands and D %% 64 == 0 (got D = %d)", D);
     return RC_EINVAL;

@@ -1,6 +1,12 @@
 #!/usr/bin/env python3
 """Clocks and power while ONE kernel family runs back to back for about a second each: the tensor-core build (from
-packed features), the lookup, and a plain memset -- does the 1 kW cap pace them?  nvidia-smi sampled every 10 ms."""
+packed features), the lookup, a plain memset and a cuBLAS bf16 GEMM -- does the 1 kW cap pace them, and what does a
+launch cost in joules (mean power x time)?  nvidia-smi sampled every 10 ms.
+
+    python tools/power_probe.py [case ...]          # default: all cases
+    RAFTCORR_LIB=raft_stir_b200/_build/attrib/libraftcorr.so RC_TC_DEBUG=8 python tools/power_probe.py build_64_pairs_nhwc16
+      (the attribution build, python -m raft_stir_b200.build --attrib: 8 = operand loads + MMAs + TMEM reads only,
+       1 = everything but the global stores)"""
 import json
 import os
 import subprocess
@@ -41,6 +47,7 @@ class Sampler:
         cap = sum("Active" in l.split(",")[2] and "Not" not in l.split(",")[2] for l in sel)
         return {"samples": len(sel), "sm_mhz_median": sorted(clk)[len(clk) // 2] if clk else None,
                 "sm_mhz_min": min(clk) if clk else None, "power_w_median": sorted(pw)[len(pw) // 2] if pw else None,
+                "power_w_mean": sum(pw) / len(pw) if pw else None,
                 "power_w_max": max(pw) if pw else None, "sw_power_cap_samples": cap}
 
 
@@ -52,9 +59,16 @@ with torch.no_grad():
         "build_64_pairs_nhwc16": lambda: R.CorrBlock(p1, p2, 4, 4),
         "lookup_64_pairs": lambda: blk(coords),
         "zero_2GiB": lambda: big.zero_(),
+        "cublas_bf16_8192": lambda: torch.matmul(ga, gb, out=gc),
     }
     big = torch.empty(1 << 31, dtype=torch.uint8, device=dev)
+    ga = torch.randn(8192, 8192, device=dev, dtype=torch.bfloat16)
+    gb = torch.randn(8192, 8192, device=dev, dtype=torch.bfloat16)
+    gc = torch.empty(8192, 8192, device=dev, dtype=torch.bfloat16)
+    want = sys.argv[1:] or list(cases)
     for name, fn in cases.items():
+        if name not in want:
+            continue
         fn(); torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         reps = 0
@@ -67,8 +81,11 @@ with torch.no_grad():
             torch.cuda.synchronize()
         e1.record(); torch.cuda.synchronize()
         t1 = time.perf_counter()
-        out = {"case": name, "reps": reps, "avg_ms": e0.elapsed_time(e1) / reps}
+        out = {"case": name, "lib": os.environ.get("RAFTCORR_LIB", "default"), "RC_TC_DEBUG": os.environ.get("RC_TC_DEBUG", "0"),
+               "RC_BUILD_PAIR": os.environ.get("RC_BUILD_PAIR", "1"), "reps": reps, "avg_ms": e0.elapsed_time(e1) / reps}
         out.update(s.window(t0 + 0.3, t1))
+        if out["power_w_mean"]:
+            out["joule_per_call"] = out["power_w_mean"] * out["avg_ms"] * 1e-3
         print(json.dumps(out), flush=True)
         time.sleep(0.5)
 s.p.terminate()
