@@ -148,9 +148,13 @@ constexpr int STEP_BYTES = 32 * 128;      // per-warp level-0 step buffer
 constexpr int L1BUF_BYTES = 32 * 128;     // per-warp level-1 buffer (bf16 uses half)
 constexpr int STAGE_BYTES_PER_WARP = STEP_BYTES + L1BUF_BYTES;
 // The same for the epilogue that stores with TMA (CTA pairs, 2-byte storage): two level-0 step buffers (a step's bulk
-// store drains while the next step is computed), two level-1 buffers (tile parity), 1 KB for the level-2/3 exchange.
-constexpr int TS_L1_OFF = 2 * STEP_BYTES, TS_L1_BYTES = 2048, TS_XQ_OFF = TS_L1_OFF + 2 * TS_L1_BYTES;
-constexpr int TS_BYTES_PER_WARP = TS_XQ_OFF + 1024;          // 13 KB
+// store drains while the next step is computed) and one level-1 buffer per warp, then 1 KB per TMEM quarter for the
+// level-2/3 exchange behind all warps' buffers.  Every KB saved here is ring depth: the operand loads share L2 and the
+// TMA unit with the output stream and need >= 64 KB in flight per SM.
+constexpr int TS_L1_OFF = 2 * STEP_BYTES, TS_L1_BYTES = 2048;
+constexpr int TS_BYTES_PER_WARP = TS_L1_OFF + TS_L1_BYTES;  // 10 KB
+constexpr int TS_XQ_OFF = EPI_WARPS * TS_BYTES_PER_WARP, TS_XQ_BYTES = 4 * 1024;
+constexpr int TS_BYTES = TS_XQ_OFF + TS_XQ_BYTES;            // 84 KB
 
 __device__ __forceinline__ void sts16(uint32_t addr, uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
@@ -174,6 +178,11 @@ __device__ __forceinline__ void put_unit(uint32_t addr, const float *v) {
 // Read-back of such a buffer and coalesced store, one full 32-byte sector per lane (st.global.v8): 4 lanes cover one
 // query's 128 bytes, 8 queries per instruction.  `sbuf`: the buffer's base; lane = (query within 8) * 4 + unit pair;
 // g: this lane's global address for its first query.  (With 16-byte stores the kernel was 4 % slower.)
+// an empty volatile statement that "rewrites" 16 registers: later uses cannot be scheduled above it
+__device__ __forceinline__ void pin_regs(uint32_t (&r)[16]) {
+  asm volatile("" : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]), "+r"(r[8]),
+                    "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]));
+}
 __device__ __forceinline__ void named_bar_arrive(uint32_t id, uint32_t count) {
   asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory");
 }
@@ -245,7 +254,7 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
   const uint32_t sA = smem_u32(smem);
   const uint32_t sB = TF32 ? sA : sA + p.KB * A_KB_BYTES;
   const uint32_t sStage = sB + p.stages * SLOT;
-  const uint32_t sBar = sStage + EPI_WARPS * WSTAGE;
+  const uint32_t sBar = sStage + (TMAST ? TS_BYTES : EPI_WARPS * STAGE_BYTES_PER_WARP);
   uint32_t *tmem_slot = (uint32_t *)(smem + (sBar - sA) + 240);
   // barrier table (8 bytes each)
   const uint32_t bar_a_full = sBar, bar_a_empty = sBar + 8;
@@ -312,6 +321,13 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
           }
           a_loaded = true;
           cur_key = key;
+        }
+        // The query operand of the NEXT query block is read by nobody else, so its load would come from DRAM while the
+        // MMAs wait: three tiles ahead, ask L2 to fetch it (if this walker's range reaches that block).
+        if (!TF32 && n == (p.NT > 3 ? p.NT - 3 : 0) && walk.left >= p.NT - n) {
+          int nb = b, nm = m + 1;
+          if (nm == p.MTW) { nm = 0; ++nb; }
+          for (int kb = 0; kb < p.KB; ++kb) tma_prefetch_3d(&map_a, kb * BKE, (PAIR ? 2 * nm + (int)rank : nm) * BM, nb);
         }
         for (int kb = 0; kb < p.KB; ++kb) {
           mbar_wait(bar_b_empty + 8 * st, ph ^ 1);
@@ -437,15 +453,20 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
       mbar_wait(bar_t_full + 8 * acc, t_par);
       fence_after();
       const uint32_t taddr = tmem_base + acc * BN + group * GW + ((uint32_t)(quarter * 32) << 16);
+      // TMAST: block rows 0..3 now, rows 4..7 after the first pair of rows has been consumed (96 instead of 128
+      // accumulator registers live at the peak: with all 128 the kernel spilled, and a spill reload sat right behind
+      // this wait); the accumulator is handed back when the second half has landed.  Otherwise all 8 rows at once.
       uint32_t raw[8][GW];
 #pragma unroll
-      for (int r = 0; r < 8; ++r) tmem_ld16(taddr + r * TB_W, raw[r]);
+      for (int r = 0; r < (TMAST ? 4 : 8); ++r) tmem_ld16(taddr + r * TB_W, raw[r]);
       tmem_ld_wait();
-      fence_before();
-      __syncwarp();
-      if (lane == 0) {
-        if (PAIR) mbar_arrive_cluster(t_empty + 8 * acc);
-        else mbar_arrive(bar_t_empty + 8 * acc);
+      if (!TMAST) {
+        fence_before();
+        __syncwarp();
+        if (lane == 0) {
+          if (PAIR) mbar_arrive_cluster(t_empty + 8 * acc);
+          else mbar_arrive(bar_t_empty + 8 * acc);
+        }
       }
       // Attribution builds only (python -m raft_stir_b200.build --attrib -> _build/attrib/libraftcorr.so, RC_TC_DEBUG in
       // the environment): 1 = no global stores of levels 0/1 and no level-2/3 stores, 2 = the same, 4 = no staging
@@ -453,12 +474,24 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
       // library compiles with dbg = 0 and none of this.
 #ifdef RC_TC_ATTRIB
       const int dbg = p.debug;
-      if (dbg & 8) { asm volatile("" ::"r"(raw[0][0]), "r"(raw[7][15])); continue; }
+      if (dbg & 8) {
+        if (TMAST) {
+#pragma unroll
+          for (int r = 4; r < 8; ++r) tmem_ld16(taddr + r * TB_W, raw[r]);
+          tmem_ld_wait();
+          fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(t_empty + 8 * acc);
+        }
+        asm volatile("" ::"r"(raw[0][0]), "r"(raw[7][15]));
+        continue;
+      }
 #else
       constexpr int dbg = 0;
 #endif
 
       float p1prev[8], p2prev[4];
+      uint32_t l1keep[2][4];                            // TMA-store epilogue: level-1 rows 0 and 1, packed
       uint32_t l2w[4] = {0u, 0u, 0u, 0u}, l3w = 0u;     // 2-byte storage: this thread's level-2 rows and level-3 cells, packed
 #pragma unroll
       for (int rp = 0; rp < 4; ++rp) {
@@ -470,9 +503,20 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
           if (SCALE) { v0[k] *= p.scale; v1[k] *= p.scale; }
         }
         // ---- level 0 units of block rows 2rp, 2rp+1
+        if (TMAST && rp == 1) {
+#pragma unroll
+          for (int r = 4; r < 8; ++r) tmem_ld16(taddr + r * TB_W, raw[r]);      // in flight under this pair of rows
+        }
+        if (TMAST && rp == 2) {
+          tmem_ld_wait();
+          pin_regs(raw[4]); pin_regs(raw[5]); pin_regs(raw[6]); pin_regs(raw[7]);   // no use of these is scheduled above the wait
+          fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(t_empty + 8 * acc);
+        }
         if (TMAST && !(rp & 1)) {
-          // the bulk store that last read this step buffer (and, at the start of a tile, this tile parity's level-1
-          // buffer) has to be done with shared memory: all but the newest group
+          // the bulk store that last read this step buffer (and, at rp == 2, the level-1 buffer: the previous tile's
+          // last group) has to be done with shared memory: all but the newest group
           if (lane == 0) bulk_wait_read<1>();
           __syncwarp();
         }
@@ -500,8 +544,21 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
         }
         if (L > 1) {
           // level-1 row rp of the sub-block: bf16 one unit (row rp of its tile), fp32 two (tiles 0, 1)
-          if (ES == 2) {
-            put_unit<VolT>((TMAST ? l1_st + (acc * TS_L1_BYTES) : l1_st) ^ (rp << 4), p1);
+          if (TMAST) {
+            // one level-1 buffer: the store of the previous tile's cells is known to be done with it only after the wait
+            // at rp == 2, so rows 0 and 1 stay in registers (packed) until then
+            if (rp < 2) {
+#pragma unroll
+              for (int k = 0; k < 4; ++k) l1keep[rp][k] = pack2<VolT>(p1[2 * k], p1[2 * k + 1]);
+            } else {
+              if (rp == 2) {
+                sts16(l1_st, l1keep[0][0], l1keep[0][1], l1keep[0][2], l1keep[0][3]);
+                sts16(l1_st ^ (1 << 4), l1keep[1][0], l1keep[1][1], l1keep[1][2], l1keep[1][3]);
+              }
+              put_unit<VolT>(l1_st ^ (rp << 4), p1);
+            }
+          } else if (ES == 2) {
+            put_unit<VolT>(l1_st ^ (rp << 4), p1);
           } else {
             put_unit<VolT>(l1_st ^ (rp << 4), p1);
             put_unit<VolT>(l1_st ^ ((4 + rp) << 4), p1 + 4);
@@ -563,7 +620,7 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
             if (lane == 0) {
               if (!(dbg & 3)) tma_store_4d(&map_l0, sbuf + (rp >> 1) * STEP_BYTES, txg * 32, (y0 >> 2) + (rp >> 1), qw, b, pol_out);
               if (rp == 3 && L > 1 && !(dbg & 3))     // and the tile's level-1 cells: [32 queries][64 B], 64-byte swizzle
-                tma_store_4d(&map_l1, lbuf + acc * TS_L1_BYTES, ((xg >> 1) / S::TW) * 32, y0 >> 3, qw, b, pol_out);
+                tma_store_4d(&map_l1, lbuf, ((xg >> 1) / S::TW) * 32, y0 >> 3, qw, b, pol_out);
               bulk_commit();
             }
           }
@@ -607,7 +664,8 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
       // of its level-1 buffer ("full" = named barrier 1 + quarter, "empty" = 5 + quarter, 64 threads each: the
       // arriving warp and the waiting one); group 0 stores whole sectors.
       if (ES == 2 && L > 2 && !(dbg & 3)) {
-        const uint32_t xq = sStage + (((warp - EPI_WARP0) & 3) + 4) * WSTAGE + (TMAST ? TS_XQ_OFF : STEP_BYTES + 2048) + lane * 32;   // in the group-1 warp's buffer
+        const uint32_t xq = TMAST ? sStage + TS_XQ_OFF + quarter * 1024 + lane * 32      // behind the warps' buffers
+                                  : sStage + (((warp - EPI_WARP0) & 3) + 4) * WSTAGE + STEP_BYTES + 2048 + lane * 32;   // in the group-1 warp's buffer
         if (group == 1) {
           if (!first_tile) named_bar_sync(5 + quarter, 64);
           sts16(xq, l2w[0], l2w[1], l2w[2], l2w[3]);
@@ -755,7 +813,7 @@ int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, con
   RC_CUDA(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
   constexpr bool TMAST = PAIR && sizeof(VolT) == 2;
   const size_t fixed = (TF32 ? 0 : (size_t)p.KB * A_KB_BYTES) +
-                       (size_t)EPI_WARPS * (TMAST ? TS_BYTES_PER_WARP : STAGE_BYTES_PER_WARP) + 256 + 1024;
+                       (TMAST ? (size_t)TS_BYTES : (size_t)EPI_WARPS * STAGE_BYTES_PER_WARP) + 256 + 1024;
   p.stages = 0;
   for (int st = MAX_STAGES; st >= 2; --st)
     if (fixed + (size_t)st * SLOT <= (size_t)max_smem) {
