@@ -29,6 +29,8 @@
 #include <cuda.h>
 #include <stdlib.h>
 
+#include <atomic>
+
 #include "common.cuh"
 #include "tc_ptx.cuh"
 
@@ -299,7 +301,9 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
   if (warp == 0) {
     // ===================================================== TMA producer
     if (lane == 0) {
-      const uint64_t pol_in = l2_policy_evict_last();
+      const uint64_t pol_in = l2_policy_evict_last();      // target blocks: every query block of the pair re-reads them
+      // the stationary query operand is read ONCE (by this CTA): it must not compete with the target blocks for L2
+      const uint64_t pol_a = TF32 ? pol_in : l2_policy_evict_first();
       // where this CTA's loads report: its own "full" barriers, or the leader's
       const uint32_t full_a = PAIR ? mapa_shared(bar_a_full, 0) : bar_a_full;
       const uint32_t full_b = PAIR ? mapa_shared(bar_b_full, 0) : bar_b_full;
@@ -316,8 +320,8 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
           if (a_loaded) { mbar_wait(bar_a_empty, a_par); a_par ^= 1; }
           if (rank == 0) mbar_expect_tx(bar_a_full, CTAS * p.KB * A_KB_BYTES);
           for (int kb = 0; kb < p.KB; ++kb) {
-            if (PAIR) tma_load_3d_2sm(sA + kb * A_KB_BYTES, &map_a, full_a, kb * BKE, mq, b, pol_in);
-            else tma_load_3d(sA + kb * A_KB_BYTES, &map_a, bar_a_full, kb * BKE, mq, b, pol_in);
+            if (PAIR) tma_load_3d_2sm(sA + kb * A_KB_BYTES, &map_a, full_a, kb * BKE, mq, b, pol_a);
+            else tma_load_3d(sA + kb * A_KB_BYTES, &map_a, bar_a_full, kb * BKE, mq, b, pol_a);
           }
           a_loaded = true;
           cur_key = key;
@@ -843,8 +847,17 @@ int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, con
     qa.val.clusterDim.z = 1;
     q.attrs = &qa;
     q.numAttrs = 1;
+    // asked once per kernel instantiation, device and shared-memory size (the query costs more than the tensor maps)
+    static std::atomic<long long> cached{-1};                  // (device << 48) | (smem << 16) | clusters
+    const long long key = ((long long)dev << 48) | ((long long)smem << 16);
+    long long c = cached.load(std::memory_order_relaxed);
     int clusters = 0;
-    RC_CUDA(cudaOccupancyMaxActiveClusters(&clusters, kern, &q));
+    if (c >= 0 && (c & ~0xffffLL) == key) {
+      clusters = (int)(c & 0xffff);
+    } else {
+      RC_CUDA(cudaOccupancyMaxActiveClusters(&clusters, kern, &q));
+      cached.store(key | (clusters & 0xffff), std::memory_order_relaxed);
+    }
     walkers = clusters < sms / 2 ? clusters : sms / 2;
     if (walkers < 1) {
       set_error("the device cannot co-schedule a CTA pair of the tensor-core build (set RC_BUILD_PAIR=0)");
@@ -852,10 +865,20 @@ int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, con
     }
   }
 
-  // pairs per group: about one query block's worth of tiles per walker and group
+  // Pairs per group.  All walkers enter a group together and miss L2 on its operands together, so groups should be
+  // few; but a group's operands have to stay in L2 next to the output stream.  Measured at the Sintel shape, 64 pairs
+  // (7.2 MB of 16-bit operands per pair, `tools/gpu_group.sh`): 3 pairs per group 2.37 ms, 4: 2.24-2.39, 8: 2.26, 11 or
+  // more: 2.35 with twice the DRAM reads (79 MB no longer stay).  So: as many pairs as fit 60 MB, and at least about
+  // one query block's worth of tiles per walker.
   const long long tpp = (long long)p.MTW * p.NT;
   long long gp = ((long long)p.NT * walkers + tpp - 1) / tpp;
+  const long long pair_operand_bytes = ((long long)N + rows2) * D * OPB;
   if (TF32) gp = (gp + 1) / 2;            // fp32 operands: twice the bytes to keep hot in L2 per pair
+  // (with 4-byte storage the output stream is twice as wide and the larger groups were slower: 5.71 against 5.49 ms)
+  if (TMAST && 60000000LL / pair_operand_bytes > gp) gp = 60000000LL / pair_operand_bytes;
+#ifdef RC_TC_ATTRIB
+  { const char *e = getenv("RC_TC_GROUP"); if (e) gp = atoi(e); }
+#endif
   if (gp < 1) gp = 1;
   if (gp > B) gp = B;
   p.group_pairs = (int)gp;

@@ -92,6 +92,75 @@ pack_features_kernel(const float *__restrict__ fmap1, const float *__restrict__ 
   }
 }
 
+// 16-bit outputs: one block = 64 consecutive output rows x ALL channels, so that every output row (D * 2 bytes, 512 for
+// D = 256) leaves whole, as consecutive 128-byte stores of one warp, and every channel is read in 256-byte runs.  (The
+// 64-channel tiles above write 128-byte pieces of a row from four blocks that run at different times.)  The transpose
+// goes through shared memory as packed channel PAIRS: tile[c][r] = (in[2c][r], in[2c+1][r]), row pitch 65 words, both
+// the pixel-major writes and the channel-major reads conflict-free.  D <= 256, D even.
+constexpr int PW_ROWS = 64;
+constexpr int PW_MAXPAIRS = 128;
+
+template <typename OutT>
+__global__ void __launch_bounds__(256)
+pack_rows16_kernel(const float *__restrict__ fmap1, const float *__restrict__ fmap2, OutT *__restrict__ f1p,
+                   OutT *__restrict__ f2p, int D, int H, int W, int groups1, int nbx, long long rows2, float scale1) {
+  __shared__ uint32_t tile[PW_MAXPAIRS][PW_ROWS + 1];
+  const int N = H * W;
+  const int b = blockIdx.y;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const bool second = (int)blockIdx.x >= groups1;
+  const int g = second ? blockIdx.x - groups1 : blockIdx.x;
+  const long long row0 = (long long)g * PW_ROWS;
+  const int pairs = D >> 1;
+
+  // source pixels of this lane's two rows (lane, lane + 32)
+  int src[2];
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    src[h] = -1;
+    const long long r = row0 + 32 * h + lane;
+    if (!second) {
+      if (r < N) src[h] = (int)r;
+    } else {
+      const int blk = (int)(r / TB_N), rr = (int)(r % TB_N);
+      const int y = (blk / nbx) * TB_H + rr / TB_W, x = (blk % nbx) * TB_W + rr % TB_W;
+      if (r < rows2 && y < H && x < W) src[h] = y * W + x;
+    }
+  }
+  const float *in = (second ? fmap2 : fmap1) + (size_t)b * D * N;
+  const float mul = second ? 1.f : scale1;     // exact power of two (common.cuh: split_scale)
+  for (int c0 = 0; c0 < pairs; c0 += 32) {     // 4 channel pairs per warp and round, 16 loads in flight per thread
+    float v[4][2][2];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int c = c0 + wid + 8 * k;
+#pragma unroll
+      for (int h = 0; h < 2; ++h)
+#pragma unroll
+        for (int e = 0; e < 2; ++e)
+          v[k][h][e] = (c < pairs && src[h] >= 0) ? __ldg(in + (size_t)(2 * c + e) * N + src[h]) : 0.f;
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int c = c0 + wid + 8 * k;
+      if (c < pairs) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) tile[c][32 * h + lane] = pack2<OutT>(mul * v[k][h][0], mul * v[k][h][1]);
+      }
+    }
+  }
+  __syncthreads();
+  OutT *out = second ? f2p + ((size_t)b * rows2 + row0) * D : f1p + ((size_t)b * N + row0) * D;
+  const long long limit = second ? rows2 : (long long)N;
+#pragma unroll 2
+  for (int k = 0; k < PW_ROWS / 8; ++k) {
+    const int r = wid + 8 * k;
+    if (row0 + r >= limit) continue;
+    uint32_t *o = reinterpret_cast<uint32_t *>(out + (size_t)r * D);
+    for (int c = lane; c < pairs; c += 32) o[c] = tile[c][r];
+  }
+}
+
 }  // namespace
 
 int launch_pack(const float *fmap1, const float *fmap2, int B, int D, int H, int W, int math,
@@ -104,7 +173,15 @@ int launch_pack(const float *fmap1, const float *fmap2, int B, int D, int H, int
   dim3 grid(groups1 + groups2, ceil_div(D, PK_D), B);
   float pre = 1.f, post = 1.f;
   split_scale(D, &pre, &post);
-  if (math == RC_MATH_BF16) {
+  if ((math == RC_MATH_BF16 || math == RC_MATH_F16) && D % 2 == 0 && D <= 2 * PW_MAXPAIRS) {
+    const int g1 = ceil_div(N, PW_ROWS), g2 = (int)(rows2 / PW_ROWS);
+    dim3 gw(g1 + g2, B);
+    if (math == RC_MATH_BF16)
+      pack_rows16_kernel<__nv_bfloat16><<<gw, 256, 0, s>>>(fmap1, fmap2, (__nv_bfloat16 *)f1p, (__nv_bfloat16 *)f2p, D, H, W,
+                                                           g1, nbx, rows2, pre);
+    else
+      pack_rows16_kernel<__half><<<gw, 256, 0, s>>>(fmap1, fmap2, (__half *)f1p, (__half *)f2p, D, H, W, g1, nbx, rows2, pre);
+  } else if (math == RC_MATH_BF16) {
     pack_features_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>(
         fmap1, fmap2, (__nv_bfloat16 *)f1p, (__nv_bfloat16 *)f2p, D, H, W, groups1, nbx, rows2, pre);
   } else if (math == RC_MATH_F16) {
