@@ -152,11 +152,11 @@ constexpr int STAGE_BYTES_PER_WARP = STEP_BYTES + L1BUF_BYTES;
 // The same for the epilogue that stores with TMA (CTA pairs, 2-byte storage): two level-0 step buffers (a step's bulk
 // store drains while the next step is computed) and one level-1 buffer per warp, then 1 KB per TMEM quarter for the
 // level-2/3 exchange behind all warps' buffers.  Every KB saved here is ring depth: the operand loads share L2 and the
-// TMA unit with the output stream and need >= 64 KB in flight per SM.
+// TMA unit with the output stream (three stages: the epilogue waited 32 % of its time for an accumulator, four: 22 %).
 constexpr int TS_L1_OFF = 2 * STEP_BYTES, TS_L1_BYTES = 2048;
 constexpr int TS_BYTES_PER_WARP = TS_L1_OFF + TS_L1_BYTES;  // 10 KB
-constexpr int TS_XQ_OFF = EPI_WARPS * TS_BYTES_PER_WARP, TS_XQ_BYTES = 4 * 1024;
-constexpr int TS_BYTES = TS_XQ_OFF + TS_XQ_BYTES;            // 84 KB
+constexpr int TS_XQ_OFF = EPI_WARPS * TS_BYTES_PER_WARP, TS_XQ_QUARTER = 32 * 16 + 32 * 4;   // per lane 16 B + 4 B
+constexpr int TS_BYTES = TS_XQ_OFF + 4 * TS_XQ_QUARTER;      // 82.5 KB: with the 64 KB operand, FIVE 16 KB ring stages fit
 
 __device__ __forceinline__ void sts16(uint32_t addr, uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
@@ -252,6 +252,9 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
   constexpr uint32_t CTAS = PAIR ? 2 : 1;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // carve (operand offsets are multiples of 1024)
+  // The TMA-store variant needs every byte (5 ring stages leave 256 bytes) and has no slack to align itself with: the
+  // dynamic shared memory of a kernel without static shared memory starts 1024-aligned, as declared; checked, not assumed.
+  if (TMAST && (smem_u32(smem_raw) & 1023u)) __trap();
   uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const uint32_t sA = smem_u32(smem);
   const uint32_t sB = TF32 ? sA : sA + p.KB * A_KB_BYTES;
@@ -668,18 +671,19 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
       // of its level-1 buffer ("full" = named barrier 1 + quarter, "empty" = 5 + quarter, 64 threads each: the
       // arriving warp and the waiting one); group 0 stores whole sectors.
       if (ES == 2 && L > 2 && !(dbg & 3)) {
-        const uint32_t xq = TMAST ? sStage + TS_XQ_OFF + quarter * 1024 + lane * 32      // behind the warps' buffers
+        const uint32_t xq = TMAST ? sStage + TS_XQ_OFF + quarter * TS_XQ_QUARTER + lane * 16      // behind the warps' buffers
                                   : sStage + (((warp - EPI_WARP0) & 3) + 4) * WSTAGE + STEP_BYTES + 2048 + lane * 32;   // in the group-1 warp's buffer
+        const uint32_t xq3 = TMAST ? sStage + TS_XQ_OFF + quarter * TS_XQ_QUARTER + 512 + lane * 4 : xq + 16;     // its level-3 word
         if (group == 1) {
           if (!first_tile) named_bar_sync(5 + quarter, 64);
           sts16(xq, l2w[0], l2w[1], l2w[2], l2w[3]);
-          asm volatile("st.shared.b32 [%0], %1;" ::"r"(xq + 16), "r"(l3w) : "memory");
+          asm volatile("st.shared.b32 [%0], %1;" ::"r"(xq3), "r"(l3w) : "memory");
           named_bar_arrive(1 + quarter, 64);
         } else {
           named_bar_sync(1 + quarter, 64);
           const uint4 o = lds16(xq);
           uint32_t o3;
-          asm volatile("ld.shared.b32 %0, [%1];" : "=r"(o3) : "r"(xq + 16) : "memory");
+          asm volatile("ld.shared.b32 %0, [%1];" : "=r"(o3) : "r"(xq3) : "memory");
           named_bar_arrive(5 + quarter, 64);
           const int x2 = x0 >> 2, x3 = x0 >> 3;
           if (lane < nq && (y0 >> 4) < p.tiles_y[2] && x2 / S::TW < p.tiles_x[2]) {
@@ -817,7 +821,7 @@ int build_tc_t(const void *f1p, const void *f2p, int B, int D, int H, int W, con
   RC_CUDA(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
   constexpr bool TMAST = PAIR && sizeof(VolT) == 2;
   const size_t fixed = (TF32 ? 0 : (size_t)p.KB * A_KB_BYTES) +
-                       (TMAST ? (size_t)TS_BYTES : (size_t)EPI_WARPS * STAGE_BYTES_PER_WARP) + 256 + 1024;
+                       (TMAST ? (size_t)TS_BYTES : (size_t)EPI_WARPS * STAGE_BYTES_PER_WARP) + 256 + (TMAST ? 0 : 1024);
   p.stages = 0;
   for (int st = MAX_STAGES; st >= 2; --st)
     if (fixed + (size_t)st * SLOT <= (size_t)max_smem) {
