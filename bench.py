@@ -108,7 +108,7 @@ def make_inputs(batch, device, seed):
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap,power.draw")
 
     def __init__(self, index):
         self.index, self.proc, self.lines = index, None, []
@@ -136,7 +136,7 @@ class ClockSampler:
             self.proc.wait(timeout=2)
         except subprocess.TimeoutExpired:
             self.proc.kill()
-        sm, mx, reasons = [], [], set()
+        sm, mx, pw, reasons = [], [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for ln in self.lines:
             parts = [p.strip() for p in ln.split(",")]
@@ -149,8 +149,15 @@ class ClockSampler:
             for nm, v in zip(names, parts[2:6]):
                 if v.lower().startswith("active"):
                     reasons.add(nm)
+            if len(parts) > 6:
+                try:
+                    pw.append(float(parts[6]))
+                except ValueError:
+                    pass
+        # power_w: the board's draw over the same window (both hot kernels run at its power cap)
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+                "samples": len(sm), "reasons": sorted(reasons),
+                "power_w": {"median": statistics.median(pw), "max": max(pw)} if pw else None}
 
 
 def cpu_hot_path():
@@ -337,7 +344,7 @@ def main():
             "frac": look_gbs / pk["hbm_gbs"], "traffic": ncu_traffic("lookup_fwd_kernel", B, args.storage),
             "peak_source": pk["source"],
             "algorithmic_bytes_per_launch": look_bytes, "avg_launch_ms": look_avg}
-    roof_build = {"kernel": "pack_features_kernel + build_pyramid_tc_kernel", "bound": "hbm", "achieved": build_gbs,
+    roof_build = {"kernel": "pack_rows16_kernel + build_pyramid_tc_kernel (CTA pairs)", "bound": "hbm", "achieved": build_gbs,
                   "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": build_gbs / pk["hbm_gbs"],
                   "traffic": ncu_traffic("build_pyramid_tc_kernel", B, args.storage), "peak_source": pk["source"],
                   "algorithmic_bytes_per_launch": build_bytes, "avg_launch_ms": build_avg,
