@@ -102,6 +102,9 @@ RC_API int64_t rc_build_workspace_bytes(int B, int D, int H, int W, int math);
  *   workspace    : >= rc_build_workspace_bytes(...) bytes, 256-byte aligned
  * The tensor-core modes (RC_MATH_BF16 / _F16 / _TF32) need D % 8 == 0 and num_levels <= 4; other sizes
  * return RC_EINVAL before anything is launched (RC_MATH_F32 takes any D and up to RC_MAX_LEVELS levels).
+ * The tensor-core kernel runs as two-CTA clusters (tcgen05 cta_group::2); with RC_BUILD_PAIR=0 in the
+ * environment (read once, at the first build of the process) it runs its single-CTA form, which gives the same bits.
+ * If the device cannot co-schedule one such cluster the call returns RC_ECUDA and the message names that switch.
  */
 RC_API int rc_build_pyramid(const float *fmap1, const float *fmap2, int B, int D, int H, int W,
                      int num_levels, int vol_dtype, int math, void *pyramid,

@@ -1,5 +1,7 @@
 #!/usr/bin/env python3
-"""TEMP: times the NHWC16 build (no pack) at 16/64 pairs for the current RC_TC_DEBUG / RC_BUILD_PAIR."""
+"""Times the build from NHWC bf16 features (no pack in the way) at 16 and 64 Sintel pairs, CUDA events, 30 calls back to
+back, for whatever RC_BUILD_PAIR / RAFTCORR_LIB + RC_TC_DEBUG / RC_TC_GROUP the environment selects (tools/gpu_attr.sh,
+tools/gpu_group.sh).  One JSON line per batch size."""
 import json, os, sys, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import raft_stir_b200 as R
