@@ -511,6 +511,18 @@ def run_extras(R, device, args, pk):
             out["b1_build_ms"] = timeit(lambda: R.CorrBlock(f1, f2, LEVELS, RADIUS, storage=args.storage, math=args.math), 20)
             blk = R.CorrBlock(f1, f2, LEVELS, RADIUS, storage=args.storage, math=args.math)
             out["b1_lookup_ms"] = timeit(lambda: blk(coords[0]), 50)
+            if args.storage != "fp32" and args.math in ("bf16", "fp16"):
+                # the same build from 16-bit channels-last features (what a channels_last bf16 encoder emits):
+                # no pack kernel, the 8x32 blocks are cut out of NHWC by the TMA box
+                dt = torch.float16 if args.math == "fp16" else torch.bfloat16
+                p1, p2 = R.pack_features(f1, f2, dt)
+                out["b1_build_from_nhwc16_ms"] = timeit(lambda: R.CorrBlock(p1, p2, LEVELS, RADIUS, storage=args.storage), 20)
+                g64 = make_inputs(args.batch, device, seed=8)
+                q1, q2 = R.pack_features(g64[0], g64[1], dt)
+                out["b%d_build_from_nhwc16_ms" % args.batch] = timeit(lambda: R.CorrBlock(q1, q2, LEVELS, RADIUS, storage=args.storage), 5)
+                out["b%d_build_with_pack_ms" % args.batch] = timeit(
+                    lambda: R.CorrBlock(g64[0], g64[1], LEVELS, RADIUS, storage=args.storage, math=args.math), 5)
+                del g64, q1, q2
             out["b1_build_fp32_simt_ms"] = timeit(lambda: R.CorrBlock(f1, f2, LEVELS, RADIUS, storage="fp32", math="fp32"), 3)
             out["b1_build_tf32_fp32_storage_ms"] = timeit(lambda: R.CorrBlock(f1, f2, LEVELS, RADIUS, storage="fp32", math="tf32"), 10)
             out["b1_build_bf16_fp32_storage_ms"] = timeit(lambda: R.CorrBlock(f1, f2, LEVELS, RADIUS, storage="fp32", math="bf16"), 10)
