@@ -305,8 +305,6 @@ class CorrBlock:
                 check(L.rc_build_pyramid_nhwc16(f1.data_ptr(), f2.data_ptr(), _OP16[f1.dtype], self.B, self.D, self.H,
                                                 self.W, self.num_levels, self.vol_dtype, self._buf.data_ptr(),
                                                 _stream(f1)), "rc_build_pyramid_nhwc16")
-            f1.record_stream(torch.cuda.current_stream(self.device))
-            f2.record_stream(torch.cuda.current_stream(self.device))
             return
         ws_bytes = int(L.rc_build_workspace_bytes(self.B, self.D, self.H, self.W, self.math))
         if ws_bytes < 0:
@@ -316,7 +314,8 @@ class CorrBlock:
             check(L.rc_build_pyramid(f1.data_ptr(), f2.data_ptr(), self.B, self.D, self.H, self.W,
                                      self.num_levels, self.vol_dtype, self.math, self._buf.data_ptr(),
                                      ws.data_ptr(), ws_bytes, _stream(f1)), "rc_build_pyramid")
-        ws.record_stream(torch.cuda.current_stream(self.device))
+        # (ws was allocated on the current stream and the kernels run on it: the caching allocator's own stream order
+        # covers its reuse, no record_stream needed -- that call costs more host time than the launch)
 
     @property
     def corr_pyramid(self) -> List[torch.Tensor]:
@@ -383,7 +382,6 @@ class CorrBlock:
                                          self.num_levels, self.radius, packed_weight.data_ptr(), b32.data_ptr(), O,
                                          out.data_ptr(), _lib.RC_VOL_F32 if out_dtype is torch.float32 else _lib.RC_VOL_F16,
                                          ws.data_ptr(), ws_bytes, _stream(c)), "rc_lookup_convc1_fwd")
-        ws.record_stream(torch.cuda.current_stream(self.device))
         return out
 
     # --------------------------------------------------------------- backward
