@@ -239,6 +239,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=64,
                     help="frame pairs per GPU per step (BASELINE configs[2]: batch 64 Sintel-shape pairs)")
+    ap.add_argument("--total-batch", type=int, default=0,
+                    help="strong scaling: this many pairs in total, split evenly over the ranks (overrides --batch; "
+                         "SURVEY 8(d) config 3 asks for 64 total next to 64 per GPU)")
     ap.add_argument("--e2e-batch", type=int, default=0, help="frame pairs per end-to-end step (0 = the same as --batch)")
     ap.add_argument("--storage", default="bf16", choices=["bf16", "fp16", "fp32"])
     ap.add_argument("--math", default="bf16", choices=["bf16", "fp16", "tf32"], help="operand type of the tensor-core build")
@@ -269,6 +272,10 @@ def main():
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=device)
 
+    if args.total_batch:
+        if args.total_batch % world:
+            raise SystemExit(f"--total-batch {args.total_batch} does not split over {world} ranks")
+        args.batch = args.total_batch // world
     B = args.batch
     f1, f2, coords = make_inputs(B, device, seed=1000 + rank)
     stream = torch.cuda.current_stream()
@@ -476,7 +483,8 @@ def main():
             "metric": "frame_pairs_per_s_corr_hot_path_55x128x256_12iters",
             "value": world * B * args.steps / (ms * 1e-3), "unit": "pairs/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": {"bf16": "bf16", "fp16": "f16", "tf32": "tf32"}[args.math],
+            "scaling": "strong" if args.total_batch else "weak", "vs_baseline": None,
+            "dtype": {"bf16": "bf16", "fp16": "f16", "tf32": "tf32"}[args.math],
             "data": "synthetic",
             "config": {"workload": WORKLOAD, "pairs_per_gpu_per_step": B, "volume_storage": args.storage,
                        "build_math": f"{args.math} tcgen05, fp32 accumulate", "l2": "working set per step (pyramid %.0f MB) exceeds the 126 MB L2" % (B * PYR_ELEMS * es / 1e6),
