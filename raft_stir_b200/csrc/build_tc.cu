@@ -27,6 +27,7 @@
 // stage index and phase incrementally (no divisions): their per-stage overhead
 // is on the critical path of the tensor pipe.
 #include <cuda.h>
+#include <stdio.h>
 #include <stdlib.h>
 
 #include <atomic>
@@ -110,6 +111,14 @@ struct TileWalk {
 
 // PTX wrappers (mbarrier, TMA, tcgen05, L2 policies): tc_ptx.cuh
 using namespace tc;
+
+// Attribution builds (-DRC_TC_ATTRIB, RC_TC_DEBUG & 32): cycles a role spends in each of its waits, printed per CTA at the
+// end of the kernel.  The shipped library compiles RC_TIMED(x, stmt) to stmt.
+#ifdef RC_TC_ATTRIB
+#define RC_TIMED(acc, stmt) do { const long long t0_ = clock64(); stmt; (acc) += clock64() - t0_; } while (0)
+#else
+#define RC_TIMED(acc, stmt) do { stmt; } while (0)
+#endif
 
 // Instruction descriptor: D = F32 (bit 4), operand format of A and B at bits 7 and 10 (kind::f16: 0 = IEEE half,
 // 1 = bf16; kind::tf32: 2 = tf32), both K-major, N >> 3 at bit 17, M >> 4 at bit 24 (M = 256 for a CTA pair).
@@ -368,20 +377,24 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
       uint32_t st = 0, ph = 0;
       uint32_t i = 0;                        // tile counter: accumulator i & 1, its use number i >> 1
       const uint32_t a_lo = desc_lo(sA), b_lo = desc_lo(sB);
+#ifdef RC_TC_ATTRIB
+      long long w_afull = 0, w_tempty = 0, w_bfull = 0;
+      const long long t_start = clock64();
+#endif
       while (walk.next(p, b, m, n, by, bx)) {
         const int key = b * p.MTW + m;
         if (!TF32 && key != cur_key) {
-          mbar_wait(bar_a_full, a_par);
+          RC_TIMED(w_afull, mbar_wait(bar_a_full, a_par));
           a_par ^= 1;
           cur_key = key;
         }
         const uint32_t acc = i & 1;
-        mbar_wait(bar_t_empty + 8 * acc, ((i >> 1) & 1) ^ 1);
+        RC_TIMED(w_tempty, mbar_wait(bar_t_empty + 8 * acc, ((i >> 1) & 1) ^ 1));
         ++i;
         fence_after();
         const uint32_t d_tmem = tmem_base + acc * BN;
         for (int kb = 0; kb < p.KB; ++kb) {
-          mbar_wait(bar_b_full + 8 * st, ph);
+          RC_TIMED(w_bfull, mbar_wait(bar_b_full + 8 * st, ph));
           fence_after();
           const uint32_t al = TF32 ? b_lo + ((st * SLOT) >> 4) : a_lo + ((kb * A_KB_BYTES) >> 4);
           const uint32_t bl = b_lo + ((st * SLOT + (TF32 ? A_KB_BYTES : 0)) >> 4);
@@ -408,6 +421,11 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
           else umma_commit(bar_a_empty);
         }
       }
+#ifdef RC_TC_ATTRIB
+      if ((p.debug & 32) && blockIdx.x < 8)
+        printf("mma cta %d: tiles %u total %lld wait a_full %lld t_empty %lld b_full %lld\n", blockIdx.x, i,
+               clock64() - t_start, w_afull, w_tempty, w_bfull);
+#endif
     }
   } else {
     // ===================================================== epilogue (2 groups x 4 warps)
@@ -428,6 +446,10 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
     walk.init(walker, walkers);
     int b, m, n, by, bx;
     uint32_t i = 0;
+#ifdef RC_TC_ATTRIB
+    long long w_tfull = 0, w_store = 0;
+    const long long e_start = clock64();
+#endif
     while (walk.next(p, b, m, n, by, bx)) {
       const uint32_t acc = i & 1, t_par = (i >> 1) & 1;
       const bool first_tile = i == 0;
@@ -457,7 +479,7 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
       const long long tile_row0B = (long long)p.tiles_x[0] * 64;
 
       // ---- accumulator -> registers, then hand it back at once
-      mbar_wait(bar_t_full + 8 * acc, t_par);
+      RC_TIMED(w_tfull, mbar_wait(bar_t_full + 8 * acc, t_par));
       fence_after();
       const uint32_t taddr = tmem_base + acc * BN + group * GW + ((uint32_t)(quarter * 32) << 16);
       // TMAST: block rows 0..3 now, rows 4..7 after the first pair of rows has been consumed (96 instead of 128
@@ -524,7 +546,7 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
         if (TMAST && !(rp & 1)) {
           // the bulk store that last read this step buffer (and, at rp == 2, the level-1 buffer: the previous tile's
           // last group) has to be done with shared memory: all but the newest group
-          if (lane == 0) bulk_wait_read<1>();
+          if (lane == 0) RC_TIMED(w_store, bulk_wait_read<1>());
           __syncwarp();
         }
         if (ES == 2 && !(dbg & 4)) {
@@ -706,6 +728,11 @@ build_pyramid_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_
       if (lane == 0) bulk_wait_all();      // shared memory stays until the last stores have read it
       __syncwarp();
     }
+#ifdef RC_TC_ATTRIB
+    if ((p.debug & 32) && blockIdx.x < 8 && lane == 0 && (warp == 2 || warp == 7))
+      printf("epi cta %d warp %d: tiles %u total %lld wait t_full %lld store-buffer %lld\n", blockIdx.x, warp, i,
+             clock64() - e_start, w_tfull, w_store);
+#endif
   }
 
   fence_before();
