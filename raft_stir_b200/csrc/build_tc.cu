@@ -26,6 +26,14 @@
 // TMEM accumulators alternate.  The single-thread producer and MMA loops keep
 // stage index and phase incrementally (no divisions): their per-stage overhead
 // is on the critical path of the tensor pipe.
+//
+// Default form (template parameter PAIR, see the kernel's comment): two CTAs of a
+// cluster issue ONE tcgen05 cta_group::2 MMA of 256 queries x 256 targets; each
+// keeps its own query operand and accumulators and loads only half of every
+// target k-block (16 KB ring slots).  With 2-byte storage the epilogue of that
+// form hands levels 0 and 1 to TMA tensor stores out of double-buffered staging
+// (TMAST), so the output stream drains while the next rows are converted.  The
+// single-CTA form above remains behind RC_BUILD_PAIR=0 and must give the same bits.
 #include <cuda.h>
 #include <stdio.h>
 #include <stdlib.h>
