@@ -16,7 +16,8 @@
 //           O x 32 bytes, so that 324 channels cost 168 KB instead of 192
 //   D       fp32 in TMEM, two accumulators of O columns; epilogue: + bias, ReLU, lane = query -> 128-byte stores
 //
-// One persistent CTA per SM: warp 0 TMA producer (3-slot ring of 16 KB), warp 1 MMA issuer, warps 2..5 epilogue.
+// One persistent CTA per SM: warp 0 TMA producer (3-slot ring of 16 KB), warp 1 MMA issuer, warps 2..9 epilogue
+// (two per TMEM lane quarter, alternate 16-channel slices).
 // HBM-bound: per query it reads C * 2 bytes and writes O * 4 (fp32 out) or O * 2.
 #include <cuda.h>
 
@@ -34,6 +35,8 @@ constexpr int A_CHUNK = 64 * 128;             // one box: 64 channels x 64 queri
 constexpr int A_STAGE = 2 * A_CHUNK;          // 16 KB
 constexpr int STAGES = 3;
 constexpr int MAX_O = 256;
+constexpr int C1_EPI_WARPS = 8;               // two per TMEM lane quarter: each takes every other 16-channel slice
+constexpr int C1_THREADS = 32 * (2 + C1_EPI_WARPS);
 
 struct C1Params {
   int B, N, C, O;
@@ -74,7 +77,7 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map
       : "memory");
 }
 
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(C1_THREADS, 1)
 convc1_tc_kernel(const __grid_constant__ C1Maps maps, const C1Params p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -98,7 +101,7 @@ convc1_tc_kernel(const __grid_constant__ C1Maps maps, const C1Params p) {
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(bar_t_full + 8 * s, 1);
-      mbar_init(bar_t_empty + 8 * s, 4);
+      mbar_init(bar_t_empty + 8 * s, C1_EPI_WARPS);
     }
     mbar_init(bar_w, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -163,7 +166,9 @@ convc1_tc_kernel(const __grid_constant__ C1Maps maps, const C1Params p) {
     }
   } else {
     // ===================================================== epilogue: + bias, ReLU, out[b][o][q]
-    const int quarter = warp & 3;
+    // The epilogue is the long pole of this kernel (MMAs of a tile: 1.4 us; 256 scattered 128-byte stores per query
+    // quarter behind 16 TMEM round trips: 7 us with one warp per quarter), so two warps share each quarter.
+    const int quarter = warp & 3, half = (warp - 2) >> 2;
     uint32_t i = 0;
     for (long long idx = blockIdx.x; idx < p.total; idx += gridDim.x) {
       const int b = (int)(idx / p.mt), m = (int)(idx - (long long)b * p.mt);
@@ -174,7 +179,7 @@ convc1_tc_kernel(const __grid_constant__ C1Maps maps, const C1Params p) {
       mbar_wait(bar_t_full + 8 * acc, t_par);
       fence_after();
       const uint32_t taddr = tmem_base + acc * MAX_O + ((uint32_t)(quarter * 32) << 16);
-      for (int c = 0; c < p.O; c += 16) {
+      for (int c = 16 * half; c < p.O; c += 32) {
         uint32_t v[16];
         tmem_ld16(taddr + c, v);
         tmem_ld_wait();
@@ -267,7 +272,7 @@ int launch_convc1(const void *samples, const void *w16, const float *bias, int B
   RC_REQUIRE(smem <= (size_t)max_smem, "rc_lookup_convc1_fwd: %d x %d weights do not fit in shared memory", O, C);
   RC_CUDA(cudaFuncSetAttribute(convc1_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int grid = p.total < sms ? (int)p.total : sms;
-  convc1_tc_kernel<<<grid, 192, smem, s>>>(maps, p);
+  convc1_tc_kernel<<<grid, C1_THREADS, smem, s>>>(maps, p);
   RC_LAUNCH_CHECK("convc1_tc_kernel");
   return RC_OK;
 }
