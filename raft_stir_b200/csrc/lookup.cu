@@ -292,6 +292,12 @@ lookup_fwd_kernel(const VolT *__restrict__ pyr, const float *__restrict__ coords
   }
 }
 
+// words of tap-gradient staging per query of a level of the gradient pyramid (see lookup_bwd_kernel)
+template <typename G_>
+__host__ __device__ __forceinline__ int bwd_level_words(int Hl) { return Hl < G_::T ? Hl * G_::ROWW : G_::WPQ; }
+// word offset of every level's staging inside the backward kernel's dynamic shared memory
+struct BwdOffsets { int off[RC_MAX_LEVELS]; };
+
 // Backward.  Same decomposition, one warp per level.
 //   A. (only if d/dcoords is wanted) stage the forward windows as in the forward.
 //   B. lane == query: fold the (2r+1)^2 output gradients into the (2r+2)^2 tap
@@ -306,7 +312,8 @@ template <typename VolT, int R>
 __global__ void __launch_bounds__(32 * RC_MAX_LEVELS)
 lookup_bwd_kernel(const VolT *__restrict__ pyr, const float *__restrict__ coords,
                   const float *__restrict__ grad_out, float *__restrict__ gpyr,
-                  float *__restrict__ gcoords, Levels lv, Levels glv, int N, int strips_per_pair) {
+                  float *__restrict__ gcoords, Levels lv, Levels glv, const __grid_constant__ BwdOffsets bo, int N,
+                  int strips_per_pair) {
   using W_ = Win<VolT, R>;     // forward window in the volume's layout
   using G_ = Win<float, R>;    // tap gradients in the fp32 gradient pyramid's layout
   constexpr int T = W_::T, NW = W_::NW;
@@ -316,9 +323,13 @@ lookup_bwd_kernel(const VolT *__restrict__ pyr, const float *__restrict__ coords
   const int l = threadIdx.x >> 5;
   const bool want_dc = gcoords != nullptr;
   const bool want_vol = gpyr != nullptr;
-  const int gwin_words = want_vol ? 32 * G_::WPQ : 0;
-  const int per_level = gwin_words + (want_dc ? W_::WIN_BYTES / 4 : 0);     // words
-  uint32_t *gwin = smem_u + (size_t)l * per_level;
+  // A level with fewer rows than a window has taps (Hl < T: the coarsest level of the usual shapes) parks its tap
+  // gradients by MAP row (Hl rows per query) instead of by window row (T rows): half the staging at the FlyingChairs
+  // and Sintel shapes' level 3, which is what lets a fourth CTA live on an SM (54 instead of 61 KB).
+  const int gHl = glv.H[l];
+  const bool short_level = gHl < T;                       // warp-uniform
+  const int gwin_words = want_vol ? 32 * bwd_level_words<G_>(gHl) : 0;
+  uint32_t *gwin = smem_u + bo.off[l];
   const uint32_t win = (uint32_t)__cvta_generic_to_shared(gwin + gwin_words);
 
   const int b = blockIdx.x / strips_per_pair;
@@ -400,10 +411,12 @@ lookup_bwd_kernel(const VolT *__restrict__ pyr, const float *__restrict__ coords
         for (int i = 0; i < T; ++i) trow[i] = w.ay * hg_prev[i];
       }
       if (want_vol) {
+        const int srow = short_level ? w.y0 + j : j;                 // staged row: the map row, or the window row
+        const bool row_staged = !short_level || (unsigned)srow < (unsigned)gHl;
 #pragma unroll
         for (int i = 0; i < T; ++i) {
           if (og + i < G_::ROWW) {
-            gwin[smem_word<G_>(j * G_::ROWW + og + i, lane)] = __float_as_uint(trow[i]);
+            if (row_staged) gwin[smem_word<G_>(srow * G_::ROWW + og + i, lane)] = __float_as_uint(trow[i]);
           } else {
             // the one tap beyond the staged units (og == 3, last tap): this lane owns it
             const int yy = w.y0 + j, xx = w.x0 + i;
@@ -417,7 +430,41 @@ lookup_bwd_kernel(const VolT *__restrict__ pyr, const float *__restrict__ coords
   __syncwarp();
 
   // ---- C
-  if (want_vol) {
+  if (want_vol && short_level) {
+    const int sl = gHl * G_::NCOL;                // units per query: (map row, unit column)
+    for (int grp = 0; grp < 2; ++grp) {
+      for (int it = 0; it < (16 * sl + 31) / 32; ++it) {      // every lane runs every round (the shuffles need all of them)
+        const int s_raw = it * 32 + lane;
+        const bool valid = s_raw < 16 * sl;                   // 16 * sl need not be a multiple of 32
+        const int s = valid ? s_raw : 0;
+        const int ql = s / sl;
+        const int slot = s - ql * sl;
+        const int yy = slot / G_::NCOL;
+        const int c = slot - yy * G_::NCOL;
+        const int qq = grp * 16 + ql;
+        const int x0 = __shfl_sync(0xffffffffu, w.x0, qq);
+        const int y0 = __shfl_sync(0xffffffffu, w.y0, qq);
+        const int tc = (x0 >> G_::LOG_EPV) + c;
+        const bool ok = valid && (unsigned)(yy - y0) < (unsigned)T && (unsigned)tc < (unsigned)gg.tiles_x;
+        const long long unit = ((long long)(yy >> 2) * gg.tiles_x + tc) * 4 + (yy & 3);
+        float *ptr = glvl + (slab0 + qq) * gg.slab + unit * G_::EPV;
+        const int base = (slot * 4) * 32 + ((qq * G_::K + slot) & 31);
+        const int xb = tc * G_::EPV;
+        const int i0 = xb - x0;
+        float f[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int i = i0 + e;
+          const bool in = ok && i >= 0 && i < T && xb + e < gg.Wl;
+          f[e] = in ? __uint_as_float(gwin[base + 32 * e]) : 0.f;
+        }
+        if (ok)
+          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(ptr), "f"(f[0]), "f"(f[1]), "f"(f[2]),
+                       "f"(f[3])
+                       : "memory");
+      }
+    }
+  } else if (want_vol) {
 #pragma unroll 1
     for (int grp = 0; grp < 2; ++grp) {
 #pragma unroll 5
@@ -510,14 +557,18 @@ int lookup_bwd_t(const VolT *pyr, const float *coords, const float *grad_out, co
   using G_ = Win<float, R>;
   const int N = lay.N;
   const int strips = ceil_div(N, 32);
-  const size_t per_level = (gpyr ? (size_t)32 * G_::WPQ * 4 : 0) + (gcoords ? (size_t)W_::WIN_BYTES : 0);
-  const size_t smem = (size_t)lay.num_levels * per_level;
+  BwdOffsets bo{};
+  size_t smem = 0;
+  for (int l = 0; l < lay.num_levels; ++l) {
+    bo.off[l] = (int)(smem / 4);
+    smem += (gpyr ? (size_t)32 * bwd_level_words<G_>(glay.H[l]) * 4 : 0) + (gcoords ? (size_t)W_::WIN_BYTES : 0);
+  }
   auto kern = lookup_bwd_kernel<VolT, R>;
   static std::atomic<int> limit_set[64];
   const size_t max_smem = (size_t)RC_MAX_LEVELS * ((size_t)32 * G_::WPQ * 4 + (size_t)W_::WIN_BYTES);
   if (int r = raise_smem_limit_once((const void *)kern, max_smem, limit_set)) return r;
   kern<<<lay.B * strips, 32 * lay.num_levels, smem, s>>>(pyr, coords, grad_out, gpyr, gcoords,
-                                                         to_levels(lay), to_levels(glay), N, strips);
+                                                         to_levels(lay), to_levels(glay), bo, N, strips);
   RC_LAUNCH_CHECK("lookup_bwd_kernel");
   return RC_OK;
 }
